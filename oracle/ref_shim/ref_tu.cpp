@@ -24,6 +24,7 @@
 #include <sys/stat.h>
 #include <unistd.h>
 #include <fcntl.h>
+#include <malloc.h>
 #include <algorithm>
 #include <random>
 #include <memory>
@@ -106,6 +107,10 @@ void ref_set_core_count(int c) { pt_shim_core_count = c; }
 int ref_load(const char *run_dir, int world1, int W, int H, int pp, int flags, unsigned scene_seed)
 {
     if (world1 < 1 || world1 > (int)WORLD_KIND_COUNT) return -1;
+    /* GenerateAccelerationStructure never zeroes its 21 MB scratch grid (main.cpp:1208) and only works
+       when malloc hands back fresh zero pages; pin the mmap threshold so big blocks always are. */
+    static bool s_mallopt = false;
+    if (!s_mallopt) { mallopt(M_MMAP_THRESHOLD, 1 << 20); s_mallopt = true; }
     if (run_dir && run_dir[0] && chdir(run_dir) != 0) return -2;
     world_kind_t kind = (world_kind_t)(world1 - 1);
 
@@ -419,6 +424,7 @@ int main(int argc, char **argv)
 {
     __argc = argc;
     __argv = argv;
+    mallopt(M_MMAP_THRESHOLD, 1 << 20);   /* see ref_load */
     if (const char *s = getenv("PT_REF_SEED")) ref_seed((unsigned)strtoul(s, nullptr, 10));
     if (const char *s = getenv("PT_REF_CORES")) pt_shim_core_count = atoi(s);
     int rc = ref_main();
