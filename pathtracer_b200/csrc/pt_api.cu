@@ -1,0 +1,578 @@
+// C-ABI of libpt_b200.so (include/pt_api.h): context, scene upload (+ BVH build), render, resolve,
+// readback, multi-GPU helpers and the parity/debug exports.  CUDA only -- there is no CPU fallback;
+// pt_create fails with PT_ERR_NO_DEVICE when no device is usable.
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "pt_api.h"
+#include "pt_bvh.h"
+#include "pt_device.cuh"
+#include "pt_kernels.cuh"
+#include "pt_lbvh.cuh"
+#include "pt_wavefront.cuh"
+
+static thread_local std::string g_create_error;
+
+struct DeviceBuffer {
+    void *p = nullptr;
+    size_t bytes = 0;
+};
+
+struct pt_context {
+    int device = 0;
+    int bvh_builder = PT_BVH_HOST_SAH;
+    int kernel = PT_KERNEL_AUTO;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    std::string error;
+    std::vector<void *> scene_allocs;          // freed on re-upload / destroy
+    PtDeviceScene scene{};
+    bool has_scene = false;
+    // frame
+    int width = 0, height = 0;
+    float4 *accum = nullptr;
+    uint32_t *bgra = nullptr;
+    unsigned long long *counters = nullptr;    // device, 4 entries
+    uint64_t samples_accumulated = 0;
+    bool resolved = false;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool timing_valid = false;
+    uint32_t last_launches = 0;
+    uint32_t bvh_nodes = 0, bvh_prims = 0;
+    PtWavefront wf;
+    int sample_lanes_log2 = -1;                // -1 = auto
+};
+
+#define CK(call)                                                                                     \
+    do {                                                                                             \
+        cudaError_t e_ = (call);                                                                     \
+        if (e_ != cudaSuccess) {                                                                     \
+            ctx->error = std::string(#call) + ": " + cudaGetErrorString(e_);                         \
+            return e_ == cudaErrorMemoryAllocation ? PT_ERR_OOM : PT_ERR_CUDA;                       \
+        }                                                                                            \
+    } while (0)
+
+static int fail(pt_context *ctx, int code, const std::string &msg) {
+    if (ctx) ctx->error = msg;
+    else g_create_error = msg;
+    return code;
+}
+
+extern "C" int pt_api_version(void) { return PT_API_VERSION; }
+
+extern "C" const char *pt_last_error(const pt_context *ctx) { return ctx ? ctx->error.c_str() : g_create_error.c_str(); }
+
+extern "C" int pt_create(const pt_config *cfg, pt_context **out) {
+    if (!out) return fail(nullptr, PT_ERR_INVALID_ARG, "pt_create: out is NULL");
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+        return fail(nullptr, PT_ERR_NO_DEVICE, std::string("pt_create: no CUDA device (") + cudaGetErrorString(e) +
+                                                   "); this library has no CPU fallback");
+    int dev = cfg ? cfg->device : 0;
+    if (dev < 0 || dev >= n) return fail(nullptr, PT_ERR_INVALID_ARG, "pt_create: device ordinal out of range");
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, dev) != cudaSuccess) return fail(nullptr, PT_ERR_CUDA, "cudaGetDeviceProperties failed");
+    if (prop.major < 10)
+        return fail(nullptr, PT_ERR_NO_DEVICE, "pt_create: kernels are built for sm_100a only; device is sm_" +
+                                                   std::to_string(prop.major) + std::to_string(prop.minor));
+    pt_context *ctx = new pt_context();
+    ctx->device = dev;
+    if (cfg) { ctx->bvh_builder = cfg->bvh_builder; ctx->kernel = cfg->kernel; }
+    if (cudaSetDevice(dev) != cudaSuccess) { delete ctx; return fail(nullptr, PT_ERR_CUDA, "cudaSetDevice failed"); }
+    if (cfg && cfg->stream) ctx->stream = (cudaStream_t)cfg->stream;
+    else {
+        if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return fail(nullptr, PT_ERR_CUDA, "cudaStreamCreate failed"); }
+        ctx->own_stream = true;
+    }
+    cudaEventCreate(&ctx->ev0);
+    cudaEventCreate(&ctx->ev1);
+    if (cudaMalloc(&ctx->counters, 4 * sizeof(unsigned long long)) != cudaSuccess) { delete ctx; return fail(nullptr, PT_ERR_OOM, "cudaMalloc failed"); }
+    cudaMemset(ctx->counters, 0, 4 * sizeof(unsigned long long));
+    if (const char *s = getenv("PT_SAMPLE_LANES_LOG2")) ctx->sample_lanes_log2 = atoi(s);
+    *out = ctx;
+    return PT_OK;
+}
+
+static void free_scene(pt_context *ctx) {
+    for (void *p : ctx->scene_allocs) cudaFree(p);
+    ctx->scene_allocs.clear();
+    ctx->has_scene = false;
+}
+
+static void free_frame(pt_context *ctx) {
+    if (ctx->accum) cudaFree(ctx->accum);
+    if (ctx->bgra) cudaFree(ctx->bgra);
+    ctx->accum = nullptr; ctx->bgra = nullptr;
+    ctx->width = ctx->height = 0;
+}
+
+extern "C" int pt_destroy(pt_context *ctx) {
+    if (!ctx) return PT_OK;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    free_scene(ctx);
+    free_frame(ctx);
+    ctx->wf.release();
+    if (ctx->counters) cudaFree(ctx->counters);
+    if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+    if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return PT_OK;
+}
+
+extern "C" int pt_set_stream(pt_context *ctx, void *s) {
+    if (!ctx) return PT_ERR_INVALID_ARG;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    if (ctx->own_stream) { cudaStreamDestroy(ctx->stream); ctx->own_stream = false; }
+    ctx->stream = (cudaStream_t)s;
+    return PT_OK;
+}
+
+template <typename T>
+static int upload(pt_context *ctx, const std::vector<T> &v, const T **out) {
+    *out = nullptr;
+    if (v.empty()) return PT_OK;
+    void *p = nullptr;
+    CK(cudaMalloc(&p, v.size() * sizeof(T)));
+    ctx->scene_allocs.push_back(p);
+    CK(cudaMemcpyAsync(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
+    *out = (const T *)p;
+    return PT_OK;
+}
+
+static inline void v3sub(const float *a, const float *b, float *r) { r[0] = a[0] - b[0]; r[1] = a[1] - b[1]; r[2] = a[2] - b[2]; }
+static inline void v3cross(const float *a, const float *b, float *r) {
+    r[0] = a[1] * b[2] - b[1] * a[2]; r[1] = a[2] * b[0] - b[2] * a[0]; r[2] = a[0] * b[1] - b[0] * a[1];
+}
+static inline float v3dot(const float *a, const float *b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
+
+// PtPlanar record of a triangle / quad with corner A and edges u, v (see pt_device.cuh)
+static PtPlanar make_planar(const float *A, const float *u, const float *v) {
+    float N[3], Nu[3], w[3], a1[3], b1[3];
+    v3cross(u, v, N);
+    float m = sqrtf(v3dot(N, N));                       // Normalize(N), ray_math.hpp:363-364
+    for (int k = 0; k < 3; k++) Nu[k] = N[k] / m;
+    float inv = 1.f / v3dot(N, N);
+    for (int k = 0; k < 3; k++) w[k] = inv * N[k];      // w = N/(N.N), ray_math.hpp:370
+    v3cross(v, w, a1);
+    v3cross(w, u, b1);
+    PtPlanar r;
+    r.r0 = make_float4(Nu[0], Nu[1], Nu[2], v3dot(A, Nu));
+    r.r1 = make_float4(a1[0], a1[1], a1[2], -v3dot(A, a1));
+    r.r2 = make_float4(b1[0], b1[1], b1[2], -v3dot(A, b1));
+    return r;
+}
+
+static int upload_bvh(pt_context *ctx, const ptbvh::Result &r, PtBvh *out) {
+    static_assert(sizeof(ptbvh::Node) == sizeof(PtBvhNode), "node layouts must match");
+    const ptbvh::Node *dn = nullptr;
+    int rc = upload(ctx, r.nodes, &dn);
+    if (rc) return rc;
+    out->nodes = reinterpret_cast<const PtBvhNode *>(dn);
+    out->n_nodes = (uint32_t)r.nodes.size();
+    out->n_prims = (uint32_t)r.order.size();
+    return PT_OK;
+}
+
+extern "C" int pt_upload_scene(pt_context *ctx, const pt_scene *s) {
+    if (!ctx || !s) return PT_ERR_INVALID_ARG;
+    if (s->struct_size != sizeof(pt_scene)) return fail(ctx, PT_ERR_INVALID_ARG, "pt_upload_scene: struct_size mismatch");
+    if (s->n_materials == 0 || !s->materials) return fail(ctx, PT_ERR_INVALID_ARG, "pt_upload_scene: material 0 (the sky) is required");
+    if (s->n_spheres == 0 && !(s->flags & PT_SCENE_JUST_COSINE))
+        return fail(ctx, PT_ERR_INVALID_ARG, "pt_upload_scene: spheres[0] (the sampled light) is required unless JUST_COSINE");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    free_scene(ctx);
+    PtDeviceScene D{};
+    int rc;
+
+    // --- validate material indices ---
+    auto bad_mat = [&](uint32_t m) { return m >= s->n_materials; };
+    for (uint32_t i = 0; i < s->n_spheres; i++) if (bad_mat(s->spheres[i].mat)) return fail(ctx, PT_ERR_INVALID_ARG, "sphere material out of range");
+    for (uint32_t i = 0; i < s->n_planes; i++) if (bad_mat(s->planes[i].mat)) return fail(ctx, PT_ERR_INVALID_ARG, "plane material out of range");
+    for (uint32_t i = 0; i < s->n_quads; i++) if (bad_mat(s->quads[i].mat)) return fail(ctx, PT_ERR_INVALID_ARG, "quad material out of range");
+    for (uint32_t i = 0; i < s->n_aabbs; i++) if (bad_mat(s->aabbs[i].mat)) return fail(ctx, PT_ERR_INVALID_ARG, "aabb material out of range");
+    for (uint32_t i = 0; i < s->n_triangles; i++) if (bad_mat((uint32_t)s->tri_materials[i])) return fail(ctx, PT_ERR_INVALID_ARG, "triangle material out of range");
+
+    // --- materials and per-primitive material indices ---
+    std::vector<pt_material> mats(s->materials, s->materials + s->n_materials);
+    if ((rc = upload(ctx, mats, &D.materials))) return rc;
+    D.n_materials = s->n_materials;
+    std::vector<uint32_t> sm(s->n_spheres), pm(s->n_planes), qm(s->n_quads), am(s->n_aabbs), tm(s->n_triangles);
+    for (uint32_t i = 0; i < s->n_spheres; i++) sm[i] = s->spheres[i].mat;
+    for (uint32_t i = 0; i < s->n_planes; i++) pm[i] = s->planes[i].mat;
+    for (uint32_t i = 0; i < s->n_quads; i++) qm[i] = s->quads[i].mat;
+    for (uint32_t i = 0; i < s->n_aabbs; i++) am[i] = s->aabbs[i].mat;
+    for (uint32_t i = 0; i < s->n_triangles; i++) tm[i] = (uint32_t)s->tri_materials[i];
+    if ((rc = upload(ctx, sm, &D.sphere_mat)) || (rc = upload(ctx, pm, &D.plane_mat)) || (rc = upload(ctx, qm, &D.quad_mat)) ||
+        (rc = upload(ctx, am, &D.aabb_mat)) || (rc = upload(ctx, tm, &D.tri_mat)))
+        return rc;
+
+    // --- spheres: big or few -> linear list; the rest -> BVH ---
+    std::vector<float4> all_sph(s->n_spheres);
+    for (uint32_t i = 0; i < s->n_spheres; i++) all_sph[i] = make_float4(s->spheres[i].p.x, s->spheres[i].p.y, s->spheres[i].p.z, s->spheres[i].r);
+    if ((rc = upload(ctx, all_sph, &D.all_spheres))) return rc;
+    D.n_spheres = s->n_spheres;
+    D.light = s->n_spheres ? all_sph[0] : make_float4(0, 0, 0, 0);
+    std::vector<float4> lin_sph, bvh_sph_src;
+    std::vector<uint32_t> lin_ids, bvh_src_ids;
+    {
+        std::vector<float> radii;
+        for (auto &q : all_sph) radii.push_back(q.w);
+        float median = 0.f;
+        if (!radii.empty()) { std::nth_element(radii.begin(), radii.begin() + radii.size() / 2, radii.end()); median = radii[radii.size() / 2]; }
+        for (uint32_t i = 0; i < s->n_spheres; i++) {
+            bool big = all_sph[i].w > 16.f * median;
+            if (big || s->n_spheres <= 8) { lin_sph.push_back(all_sph[i]); lin_ids.push_back(i); }
+            else { bvh_sph_src.push_back(all_sph[i]); bvh_src_ids.push_back(i); }
+        }
+        if (bvh_sph_src.size() <= 4) {      // not worth a tree
+            for (size_t k = 0; k < bvh_sph_src.size(); k++) { lin_sph.push_back(bvh_sph_src[k]); lin_ids.push_back(bvh_src_ids[k]); }
+            bvh_sph_src.clear(); bvh_src_ids.clear();
+        }
+    }
+    if ((rc = upload(ctx, lin_sph, &D.lin_spheres)) || (rc = upload(ctx, lin_ids, &D.lin_sphere_ids))) return rc;
+    D.n_lin_spheres = (uint32_t)lin_sph.size();
+
+    ctx->bvh_nodes = ctx->bvh_prims = 0;
+    if (!bvh_sph_src.empty()) {
+        std::vector<ptbvh::Box> boxes(bvh_sph_src.size());
+        for (size_t i = 0; i < boxes.size(); i++) {
+            const float4 &q = bvh_sph_src[i];
+            boxes[i].mn[0] = q.x - q.w; boxes[i].mn[1] = q.y - q.w; boxes[i].mn[2] = q.z - q.w;
+            boxes[i].mx[0] = q.x + q.w; boxes[i].mx[1] = q.y + q.w; boxes[i].mx[2] = q.z + q.w;
+        }
+        ptbvh::Result r;
+        if (ctx->bvh_builder == PT_BVH_DEVICE_LBVH) { if ((rc = pt_lbvh_build(ctx->stream, boxes, 2, r, ctx->error))) return rc; }
+        else r = ptbvh::Builder(boxes, 2).build();
+        if (r.max_depth > PT_STACK_DEPTH - 2) return fail(ctx, PT_ERR_UNSUPPORTED, "sphere BVH deeper than the traversal stack");
+        std::vector<float4> ordered(r.order.size());
+        std::vector<uint32_t> ids(r.order.size());
+        for (size_t i = 0; i < r.order.size(); i++) { ordered[i] = bvh_sph_src[r.order[i]]; ids[i] = bvh_src_ids[r.order[i]]; }
+        if ((rc = upload(ctx, ordered, &D.bvh_spheres)) || (rc = upload(ctx, ids, &D.bvh_sphere_ids)) || (rc = upload_bvh(ctx, r, &D.sphere_bvh))) return rc;
+        ctx->bvh_nodes += D.sphere_bvh.n_nodes; ctx->bvh_prims += D.sphere_bvh.n_prims;
+    }
+
+    // --- planes, quads, boxes: linear ---
+    std::vector<float4> planes(s->n_planes);
+    for (uint32_t i = 0; i < s->n_planes; i++) planes[i] = make_float4(s->planes[i].n.x, s->planes[i].n.y, s->planes[i].n.z, s->planes[i].d);
+    if ((rc = upload(ctx, planes, &D.planes))) return rc;
+    D.n_planes = s->n_planes;
+    std::vector<PtPlanar> quads(s->n_quads);
+    for (uint32_t i = 0; i < s->n_quads; i++) quads[i] = make_planar(&s->quads[i].point.x, &s->quads[i].u.x, &s->quads[i].v.x);
+    if ((rc = upload(ctx, quads, &D.quads))) return rc;
+    D.n_quads = s->n_quads;
+    std::vector<float4> aabbs(2 * (size_t)s->n_aabbs);
+    for (uint32_t i = 0; i < s->n_aabbs; i++) {
+        aabbs[2 * i] = make_float4(s->aabbs[i].min.x, s->aabbs[i].min.y, s->aabbs[i].min.z, 0.f);
+        aabbs[2 * i + 1] = make_float4(s->aabbs[i].max.x, s->aabbs[i].max.y, s->aabbs[i].max.z, 0.f);
+    }
+    if ((rc = upload(ctx, aabbs, &D.aabbs))) return rc;
+    D.n_aabbs = s->n_aabbs;
+
+    // --- triangles: BVH ---
+    if (s->n_triangles) {
+        std::vector<ptbvh::Box> boxes(s->n_triangles);
+        std::vector<PtPlanar> recs(s->n_triangles);
+        std::vector<float4> normals(s->n_triangles);
+        for (uint32_t i = 0; i < s->n_triangles; i++) {
+            const float *P = s->tri_points + 9 * (size_t)i;
+            boxes[i].reset();
+            boxes[i].grow(P); boxes[i].grow(P + 3); boxes[i].grow(P + 6);
+            float u[3], v[3];
+            v3sub(P + 3, P, u);
+            v3sub(P + 6, P, v);
+            recs[i] = make_planar(P, u, v);
+            normals[i] = make_float4(recs[i].r0.x, recs[i].r0.y, recs[i].r0.z, 0.f);
+        }
+        ptbvh::Result r;
+        if (ctx->bvh_builder == PT_BVH_DEVICE_LBVH) { if ((rc = pt_lbvh_build(ctx->stream, boxes, 4, r, ctx->error))) return rc; }
+        else r = ptbvh::Builder(boxes, 4).build();
+        if (r.max_depth > PT_STACK_DEPTH - 2) return fail(ctx, PT_ERR_UNSUPPORTED, "triangle BVH deeper than the traversal stack");
+        std::vector<PtPlanar> ordered(r.order.size());
+        for (size_t i = 0; i < r.order.size(); i++) ordered[i] = recs[r.order[i]];
+        if ((rc = upload(ctx, ordered, &D.tris)) || (rc = upload(ctx, r.order, &D.tri_ids)) || (rc = upload(ctx, normals, &D.tri_normals)) ||
+            (rc = upload_bvh(ctx, r, &D.tri_bvh)))
+            return rc;
+        ctx->bvh_nodes += D.tri_bvh.n_nodes; ctx->bvh_prims += D.tri_bvh.n_prims;
+    }
+
+    // --- textures (RGBA8 as given) ---
+    for (int i = 0; i < 4; i++) {
+        const pt_texture &t = s->textures[i];
+        if (!t.rgba8 || t.width <= 0 || t.height <= 0) continue;
+        void *p = nullptr;
+        size_t bytes = (size_t)t.width * t.height * 4;
+        CK(cudaMalloc(&p, bytes));
+        ctx->scene_allocs.push_back(p);
+        CK(cudaMemcpyAsync(p, t.rgba8, bytes, cudaMemcpyHostToDevice, ctx->stream));
+        D.tex[i].texels = (const uchar4 *)p;
+        D.tex[i].w = t.width; D.tex[i].h = t.height;
+    }
+    for (uint32_t m = 0; m < s->n_materials; m++) {
+        const pt_material &mm = s->materials[m];
+        int idx[4] = {mm.albedo_tex, mm.metalness_tex, mm.roughness_tex, mm.normal_tex};
+        for (int k = 0; k < 4; k++)
+            if (idx[k] < 0 || idx[k] > 4 || (idx[k] > 0 && !D.tex[idx[k] - 1].texels))
+                return fail(ctx, PT_ERR_INVALID_ARG, "material references a texture that was not supplied");
+    }
+    D.flags = s->flags;
+    D.cam = s->camera;
+    CK(cudaStreamSynchronize(ctx->stream));     // the host vectors above go out of scope
+    ctx->scene = D;
+    ctx->has_scene = true;
+    return PT_OK;
+}
+
+extern "C" int pt_set_camera(pt_context *ctx, const pt_camera *cam) {
+    if (!ctx || !cam) return PT_ERR_INVALID_ARG;
+    if (!ctx->has_scene) return fail(ctx, PT_ERR_NO_SCENE, "pt_set_camera: no scene uploaded");
+    ctx->scene.cam = *cam;
+    return PT_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+static int ensure_frame(pt_context *ctx, int w, int h) {
+    if (ctx->width == w && ctx->height == h && ctx->accum) return PT_OK;
+    CK(cudaStreamSynchronize(ctx->stream));
+    free_frame(ctx);
+    size_t n = (size_t)w * h;
+    CK(cudaMalloc((void **)&ctx->accum, n * sizeof(float4)));
+    CK(cudaMalloc((void **)&ctx->bgra, n * sizeof(uint32_t)));
+    CK(cudaMemsetAsync(ctx->accum, 0, n * sizeof(float4), ctx->stream));
+    CK(cudaMemsetAsync(ctx->bgra, 0, n * sizeof(uint32_t), ctx->stream));
+    ctx->width = w; ctx->height = h;
+    ctx->samples_accumulated = 0;
+    return PT_OK;
+}
+
+static uint32_t my_tile_count(uint32_t n_tiles, uint32_t rank, uint32_t count) {
+    return rank < n_tiles ? (n_tiles - rank + count - 1) / count : 0;
+}
+
+extern "C" int pt_render(pt_context *ctx, const pt_render_params *p) {
+    if (!ctx || !p) return PT_ERR_INVALID_ARG;
+    if (p->struct_size != sizeof(pt_render_params)) return fail(ctx, PT_ERR_INVALID_ARG, "pt_render: struct_size mismatch");
+    if (!ctx->has_scene) return fail(ctx, PT_ERR_NO_SCENE, "pt_render: no scene uploaded");
+    if (p->width <= 0 || p->height <= 0 || p->pp < 0 || p->pp > 1000) return fail(ctx, PT_ERR_INVALID_ARG, "pt_render: bad width/height/pp");
+    uint32_t tile_count = p->tile_count ? p->tile_count : 1;
+    if (p->tile_rank >= tile_count) return fail(ctx, PT_ERR_INVALID_ARG, "pt_render: tile_rank >= tile_count");
+    uint32_t spp = (uint32_t)p->pp * (uint32_t)p->pp;
+    uint32_t s_end = p->sample_end ? p->sample_end : spp;
+    if (s_end > spp || p->sample_begin > s_end) return fail(ctx, PT_ERR_INVALID_ARG, "pt_render: bad sample range");
+    CK(cudaSetDevice(ctx->device));
+    int rc = ensure_frame(ctx, p->width, p->height);
+    if (rc) return rc;
+    if (p->flags & PT_RENDER_CLEAR) {
+        CK(cudaMemsetAsync(ctx->accum, 0, (size_t)p->width * p->height * sizeof(float4), ctx->stream));
+        CK(cudaMemsetAsync(ctx->counters, 0, 4 * sizeof(unsigned long long), ctx->stream));
+        ctx->samples_accumulated = 0;
+    }
+    ctx->resolved = false;
+    ctx->last_launches = 0;
+
+    PtRenderArgs A{};
+    A.width = p->width; A.height = p->height; A.pp = p->pp;
+    A.s_begin = p->sample_begin; A.s_end = s_end;
+    A.tile_rank = p->tile_rank; A.tile_count = tile_count;
+    A.tiles_x = (uint32_t)(p->width + PT_TILE - 1) / PT_TILE;
+    A.tiles_y = (uint32_t)(p->height + PT_TILE - 1) / PT_TILE;
+    A.n_my_tiles = my_tile_count(A.tiles_x * A.tiles_y, p->tile_rank, tile_count);
+    A.seed = p->seed;
+    A.accum = ctx->accum;
+    A.counters = ctx->counters;
+
+    uint32_t n_samples = s_end - p->sample_begin;
+    CK(cudaEventRecord(ctx->ev0, ctx->stream));
+    if (n_samples > 0 && A.n_my_tiles > 0) {
+        int kernel = ctx->kernel == PT_KERNEL_AUTO ? PT_KERNEL_MEGA : ctx->kernel;
+        if (kernel == PT_KERNEL_WAVEFRONT) {
+            rc = ctx->wf.render(ctx->stream, ctx->scene, A, &ctx->last_launches, ctx->error);
+            if (rc) return rc;
+        } else {
+            // lanes of a warp that share a pixel: as many as the sample range allows (power of two <= 32)
+            uint32_t lS = 0;
+            while (lS < 5 && (2u << lS) <= n_samples) lS++;
+            if (ctx->sample_lanes_log2 >= 0) lS = std::min<uint32_t>(lS, (uint32_t)ctx->sample_lanes_log2);
+            A.log2_sample_lanes = lS;
+            uint32_t warps_per_tile = 1024u >> (5u - lS);                  // pixels per tile / pixels per warp
+            uint64_t warps = (uint64_t)A.n_my_tiles * warps_per_tile;
+            uint64_t blocks = (warps + 7) / 8;
+            if (blocks > 0x7fffffffull) return fail(ctx, PT_ERR_UNSUPPORTED, "pt_render: frame too large for one launch");
+            k_render<<<(unsigned)blocks, 256, 0, ctx->stream>>>(ctx->scene, A);
+            ctx->last_launches = 1;
+        }
+        CK(cudaGetLastError());
+    }
+    CK(cudaEventRecord(ctx->ev1, ctx->stream));
+    ctx->timing_valid = true;
+    // samples accounted on the host: pixels of my tiles x samples
+    uint64_t px = 0;
+    for (uint32_t j = 0; j < A.n_my_tiles; j++) {
+        uint32_t tile = p->tile_rank + j * tile_count;
+        uint32_t tx = (tile % A.tiles_x) * PT_TILE, ty = (tile / A.tiles_x) * PT_TILE;
+        uint32_t w = std::min<uint32_t>(PT_TILE, (uint32_t)p->width - tx), h = std::min<uint32_t>(PT_TILE, (uint32_t)p->height - ty);
+        px += (uint64_t)w * h;
+    }
+    ctx->samples_accumulated += px * n_samples;
+    return PT_OK;
+}
+
+extern "C" int pt_synchronize(pt_context *ctx) {
+    if (!ctx) return PT_ERR_INVALID_ARG;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return PT_OK;
+}
+
+extern "C" int pt_resolve(pt_context *ctx) {
+    if (!ctx) return PT_ERR_INVALID_ARG;
+    if (!ctx->accum) return fail(ctx, PT_ERR_NO_FRAME, "pt_resolve: nothing rendered yet");
+    CK(cudaSetDevice(ctx->device));
+    int n = ctx->width * ctx->height;
+    k_resolve<<<(n + 255) / 256, 256, 0, ctx->stream>>>(ctx->accum, ctx->bgra, n);
+    CK(cudaGetLastError());
+    ctx->resolved = true;
+    return PT_OK;
+}
+
+extern "C" int pt_readback(pt_context *ctx, uint32_t *bgra, float *accum_rgba, pt_stats *stats) {
+    if (!ctx) return PT_ERR_INVALID_ARG;
+    if (!ctx->accum) return fail(ctx, PT_ERR_NO_FRAME, "pt_readback: nothing rendered yet");
+    CK(cudaSetDevice(ctx->device));
+    size_t n = (size_t)ctx->width * ctx->height;
+    if (bgra) {
+        if (!ctx->resolved) { int rc = pt_resolve(ctx); if (rc) return rc; }
+        CK(cudaMemcpyAsync(bgra, ctx->bgra, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    if (accum_rgba) CK(cudaMemcpyAsync(accum_rgba, ctx->accum, n * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
+    unsigned long long c[4] = {0, 0, 0, 0};
+    if (stats) CK(cudaMemcpyAsync(c, ctx->counters, sizeof(c), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (stats) {
+        memset(stats, 0, sizeof(*stats));
+        stats->samples = ctx->samples_accumulated;
+        stats->rays = c[0];
+        stats->nan_retries = c[1];
+        if (ctx->timing_valid) { float ms = 0.f; if (cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1) == cudaSuccess) stats->render_ms = ms; }
+        stats->kernel_launches = ctx->last_launches;
+        stats->bvh_nodes = ctx->bvh_nodes;
+        stats->bvh_prims = ctx->bvh_prims;
+    }
+    return PT_OK;
+}
+
+extern "C" int pt_device_buffers(pt_context *ctx, void **accum, void **bgra, int32_t *w, int32_t *h) {
+    if (!ctx) return PT_ERR_INVALID_ARG;
+    if (!ctx->accum) return fail(ctx, PT_ERR_NO_FRAME, "pt_device_buffers: nothing rendered yet");
+    if (accum) *accum = ctx->accum;
+    if (bgra) *bgra = ctx->bgra;
+    if (w) *w = ctx->width;
+    if (h) *h = ctx->height;
+    return PT_OK;
+}
+
+extern "C" int pt_pack_tiles(pt_context *ctx, void *dst, uint32_t rank, uint32_t count, uint32_t *n_out) {
+    if (!ctx || !dst || count == 0 || rank >= count) return PT_ERR_INVALID_ARG;
+    if (!ctx->bgra) return fail(ctx, PT_ERR_NO_FRAME, "pt_pack_tiles: nothing rendered yet");
+    CK(cudaSetDevice(ctx->device));
+    uint32_t tiles_x = (uint32_t)(ctx->width + PT_TILE - 1) / PT_TILE, tiles_y = (uint32_t)(ctx->height + PT_TILE - 1) / PT_TILE;
+    uint32_t n = my_tile_count(tiles_x * tiles_y, rank, count);
+    if (n_out) *n_out = n;
+    if (n) k_pack_tiles<<<(n * 1024u + 255u) / 256u, 256, 0, ctx->stream>>>(ctx->bgra, (uint32_t *)dst, ctx->width, ctx->height, tiles_x, rank, count, n);
+    CK(cudaGetLastError());
+    return PT_OK;
+}
+
+extern "C" int pt_unpack_tiles(pt_context *ctx, const void *src, uint32_t rank, uint32_t count) {
+    if (!ctx || !src || count == 0 || rank >= count) return PT_ERR_INVALID_ARG;
+    if (!ctx->bgra) return fail(ctx, PT_ERR_NO_FRAME, "pt_unpack_tiles: nothing rendered yet");
+    CK(cudaSetDevice(ctx->device));
+    uint32_t tiles_x = (uint32_t)(ctx->width + PT_TILE - 1) / PT_TILE, tiles_y = (uint32_t)(ctx->height + PT_TILE - 1) / PT_TILE;
+    uint32_t n = my_tile_count(tiles_x * tiles_y, rank, count);
+    if (n) k_unpack_tiles<<<(n * 1024u + 255u) / 256u, 256, 0, ctx->stream>>>(ctx->bgra, (const uint32_t *)src, ctx->width, ctx->height, tiles_x, rank, count, n);
+    CK(cudaGetLastError());
+    return PT_OK;
+}
+
+// ---- parity / debug exports: host pointers in, host pointers out -----------------------------------
+struct ScopedDev {
+    std::vector<void *> ptrs;
+    ~ScopedDev() { for (void *p : ptrs) cudaFree(p); }
+    void *alloc(size_t bytes) { void *p = nullptr; if (cudaMalloc(&p, bytes ? bytes : 16) != cudaSuccess) return nullptr; ptrs.push_back(p); return p; }
+};
+
+extern "C" int pt_trace_rays(pt_context *ctx, uint32_t n, const float *o, const float *d, pt_hit *out) {
+    if (!ctx || !o || !d || !out) return PT_ERR_INVALID_ARG;
+    if (!ctx->has_scene) return fail(ctx, PT_ERR_NO_SCENE, "pt_trace_rays: no scene uploaded");
+    if (n == 0) return PT_OK;
+    CK(cudaSetDevice(ctx->device));
+    ScopedDev sd;
+    float *dO = (float *)sd.alloc((size_t)n * 12), *dD = (float *)sd.alloc((size_t)n * 12);
+    pt_hit *dH = (pt_hit *)sd.alloc((size_t)n * sizeof(pt_hit));
+    if (!dO || !dD || !dH) return fail(ctx, PT_ERR_OOM, "pt_trace_rays: cudaMalloc failed");
+    CK(cudaMemcpyAsync(dO, o, (size_t)n * 12, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(dD, d, (size_t)n * 12, cudaMemcpyHostToDevice, ctx->stream));
+    k_trace_rays<<<(n + 127) / 128, 128, 0, ctx->stream>>>(ctx->scene, dO, dD, dH, n);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(out, dH, (size_t)n * sizeof(pt_hit), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return PT_OK;
+}
+
+extern "C" int pt_primary_hits(pt_context *ctx, int32_t w, int32_t h, pt_hit *out) {
+    if (!ctx || !out || w <= 0 || h <= 0) return PT_ERR_INVALID_ARG;
+    if (!ctx->has_scene) return fail(ctx, PT_ERR_NO_SCENE, "pt_primary_hits: no scene uploaded");
+    CK(cudaSetDevice(ctx->device));
+    ScopedDev sd;
+    size_t n = (size_t)w * h;
+    pt_hit *dH = (pt_hit *)sd.alloc(n * sizeof(pt_hit));
+    if (!dH) return fail(ctx, PT_ERR_OOM, "pt_primary_hits: cudaMalloc failed");
+    k_primary_hits<<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>(ctx->scene, w, h, dH);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(out, dH, n * sizeof(pt_hit), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return PT_OK;
+}
+
+extern "C" int pt_trace_paths(pt_context *ctx, uint32_t n, const float *o, const float *d, uint64_t seed, float *rgb) {
+    if (!ctx || !o || !d || !rgb) return PT_ERR_INVALID_ARG;
+    if (!ctx->has_scene) return fail(ctx, PT_ERR_NO_SCENE, "pt_trace_paths: no scene uploaded");
+    if (n == 0) return PT_OK;
+    CK(cudaSetDevice(ctx->device));
+    ScopedDev sd;
+    float *dO = (float *)sd.alloc((size_t)n * 12), *dD = (float *)sd.alloc((size_t)n * 12), *dC = (float *)sd.alloc((size_t)n * 12);
+    if (!dO || !dD || !dC) return fail(ctx, PT_ERR_OOM, "pt_trace_paths: cudaMalloc failed");
+    CK(cudaMemcpyAsync(dO, o, (size_t)n * 12, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(dD, d, (size_t)n * 12, cudaMemcpyHostToDevice, ctx->stream));
+    k_trace_paths<<<(n + 127) / 128, 128, 0, ctx->stream>>>(ctx->scene, dO, dD, seed, dC, n);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(rgb, dC, (size_t)n * 12, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return PT_OK;
+}
+
+extern "C" int pt_resolve_colors(pt_context *ctx, uint32_t n, const float *rgb, uint32_t *out) {
+    if (!ctx || !rgb || !out) return PT_ERR_INVALID_ARG;
+    if (n == 0) return PT_OK;
+    CK(cudaSetDevice(ctx->device));
+    ScopedDev sd;
+    float *dC = (float *)sd.alloc((size_t)n * 12);
+    uint32_t *dB = (uint32_t *)sd.alloc((size_t)n * 4);
+    if (!dC || !dB) return fail(ctx, PT_ERR_OOM, "pt_resolve_colors: cudaMalloc failed");
+    CK(cudaMemcpyAsync(dC, rgb, (size_t)n * 12, cudaMemcpyHostToDevice, ctx->stream));
+    k_resolve_colors<<<(n + 255) / 256, 256, 0, ctx->stream>>>(dC, dB, n);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(out, dB, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return PT_OK;
+}

@@ -1,0 +1,278 @@
+// Kernels of the render core.  One persistent-per-warp "megakernel" with path regeneration does camera
+// rays -> closest hit -> shading -> per-pixel accumulation entirely in registers; resolve, parity/debug
+// and tile pack/unpack kernels are small.  (The wavefront variant lives in pt_wavefront.cuh.)
+#pragma once
+#include "pt_device.cuh"
+#include "pt_shade.cuh"
+#include "pt_trace.cuh"
+
+struct PtRenderArgs {
+    int width, height, pp;
+    uint32_t s_begin, s_end;            // sample range of the pp*pp list
+    uint32_t tile_rank, tile_count;     // this launch renders tiles t with t % tile_count == tile_rank
+    uint32_t tiles_x, tiles_y, n_my_tiles;
+    uint32_t log2_sample_lanes;         // S = lanes of a warp that share one pixel; P = 32/S pixels per warp
+    uint64_t seed;
+    float4 *accum;                      // width*height: sum r,g,b + number of samples
+    unsigned long long *counters;       // [0] rays, [1] NaN retries, [2] samples
+};
+
+// ---- camera (RenderTexel's two sampling loops, src/win32_main.cpp:1032-1170) ----------------------
+__constant__ float2 c_poisson_disk[12] = {   // main.cpp:1097-1110
+    {0.0f, 0.0f}, {-0.94201624f, -0.39906216f}, {0.94558609f, -0.76890725f}, {-0.094184101f, -0.92938870f},
+    {0.34495938f, 0.29387760f}, {-0.91588581f, 0.45771432f}, {-0.81544232f, -0.87912464f},
+    {-0.38277543f, 0.27676845f}, {0.97484398f, 0.75648379f}, {0.44323325f, -0.97511554f},
+    {0.53742981f, -0.47373420f}, {-0.26496911f, -0.41893023f}};
+
+// Camera ray of sample s of pixel (x,y); leaves rng positioned after the camera's own draws.
+__device__ __forceinline__ void pt_camera_ray(const pt_camera &c, int W, int H, int pp, int x, int y, uint32_t s,
+                                              uint32_t retry, uint64_t seed, PtRng &rng, float3 &o, float3 &d) {
+    const float fy = -1.0f + 2.0f * (float)y / (float)H;      // row 0 = bottom; pixel -> its lower-left corner
+    const float fx = -1.0f + 2.0f * (float)x / (float)W;
+    const uint32_t pixel = (uint32_t)y * (uint32_t)W + (uint32_t)x;
+    const float3 ax = f3(c.axis_x), ay = f3(c.axis_y), fc = f3(c.frustum_center), pos = f3(c.pos);
+    rng.init(seed, pixel, s, retry << 8);
+    if (c.use_pinhole) {
+        // stratum (i,j): origins advance by hpw/pp, each stratum is 2*hpw/pp wide (main.cpp:1044-1057)
+        const uint32_t i = s / (uint32_t)pp, j = s - i * (uint32_t)pp;
+        const float inv_pp = 1.f / (float)pp;
+        const float stepX = inv_pp * c.half_pixel_w * 2.f, stepY = inv_pp * c.half_pixel_h * 2.f;
+        float xs = (fx - c.half_pixel_w) + (float)i * inv_pp * c.half_pixel_w + stepX * 0.5f;
+        float ys = (fy - c.half_pixel_h) + (float)j * inv_pp * c.half_pixel_h + stepY * 0.5f;
+        xs += (rng.next() - 0.5f) * stepX;
+        ys += (rng.next() - 0.5f) * stepY;
+        float3 P = fc + (xs * c.half_film_w) * ax + (ys * c.half_film_h) * ay;
+        o = pos;
+        d = normalize3(P - pos);
+    } else {
+        // outer film sample ri jittered +-1 pixel, focal point on the focal plane, lens point from the
+        // Poisson table at (ri*r2) % 12 (main.cpp:1114-1161)
+        const uint32_t ri = s / (uint32_t)pp, r2 = s - ri * (uint32_t)pp;
+        uint4 fj = philox4x32_10(0u, pixel, ri, 1u, (uint32_t)seed, (uint32_t)(seed >> 32));
+        float offX = fx + (2.0f * u32_to_unit(fj.x) - 1.0f) * c.half_pixel_w;
+        float offY = fy + (2.0f * u32_to_unit(fj.y) - 1.0f) * c.half_pixel_h;
+        float3 P = fc + (offX * c.half_film_w) * ax + (offY * c.half_film_h) * ay;
+        float3 dir = normalize3(P - pos);
+        const float fpd = 1.f / (1.f / 0.098f - 1.f / c.focal_length);       // == focal_distance
+        const float3 N = -f3(c.axis_z);
+        const float3 pp0 = pos + ax + fpd * N;
+        float t = __fdividef(dot3(N, pp0) - dot3(N, pos), dot3(N, dir));
+        float3 focal = pos + t * dir;
+        float2 ds = c_poisson_disk[(r2 * ri) % 12u];
+        o = pos + (ds.x * c.aperture_radius) * ax + (ds.y * c.aperture_radius) * ay;
+        d = normalize3(focal - o);
+    }
+}
+
+// ---- the render megakernel -----------------------------------------------------------------------
+// A warp owns P = 32/S adjacent pixels; the S lanes of a pixel stride through its sample list.  Every
+// loop iteration each live lane advances its path by ONE segment (trace + shade); a lane whose path
+// ended starts its next sample in the same iteration (path regeneration), so lanes at different
+// depths share the instruction stream instead of idling behind the longest path.
+__global__ void __launch_bounds__(256)
+k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRenderArgs A) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint32_t lS = A.log2_sample_lanes, lP = 5u - lS;
+    const uint32_t Sn = 1u << lS;
+    const uint32_t pw_log2 = (lP + 1u) >> 1, ph_log2 = lP - pw_log2;     // pixel block of a warp: pw x ph
+    const uint32_t groups_x_log2 = 5u - pw_log2;                          // 32/pw groups per tile row
+    const uint32_t groups_per_tile_log2 = 10u - lP;
+
+    const uint32_t tile_j = warp >> groups_per_tile_log2;
+    const uint32_t grp = warp & ((1u << groups_per_tile_log2) - 1u);
+    bool active = tile_j < A.n_my_tiles;
+    const uint32_t tile = A.tile_rank + tile_j * A.tile_count;
+    const uint32_t tx = (tile % A.tiles_x) * PT_TILE, ty = (tile / A.tiles_x) * PT_TILE;
+    const uint32_t gx = grp & ((1u << groups_x_log2) - 1u), gy = grp >> groups_x_log2;
+    const uint32_t pig = lane >> lS, sl = lane & (Sn - 1u);
+    const int x = (int)(tx + (gx << pw_log2) + (pig & ((1u << pw_log2) - 1u)));
+    const int y = (int)(ty + (gy << ph_log2) + (pig >> pw_log2));
+    active = active && x < A.width && y < A.height;
+
+    uint32_t s = active ? A.s_begin + sl : A.s_end;
+    uint32_t retry = 0, n_acc = 0, n_rays = 0, n_nan = 0;
+    float3 acc = f3(0, 0, 0);
+    float3 o = f3(0, 0, 0), d = f3(0, 0, 1), beta = f3(1, 1, 1), L = f3(0, 0, 0);
+    int depth = 0;
+    bool alive = false;
+    PtRng rng;
+    rng.init(A.seed, 0, 0, 0);
+
+    while (true) {
+        if (!alive && s < A.s_end) {
+            pt_camera_ray(S.cam, A.width, A.height, A.pp, x, y, s, retry, A.seed, rng, o, d);
+            beta = f3(1, 1, 1);
+            L = f3(0, 0, 0);
+            depth = 0;
+            alive = true;
+        }
+        if (!__any_sync(0xffffffffu, alive)) break;
+        if (alive) {
+            PtHit h = pt_closest_hit(S, o, d);
+            n_rays++;
+            float3 n;
+            uint32_t mat;
+            pt_hit_surface(S, h, o, d, n, mat);
+            float3 e = pt_load_emit(S, mat);
+            L = L + beta * e;                                               // radiance += emitColor, main.cpp:799
+            bool emissive = (e.x != 0.f) || (e.y != 0.f) || (e.z != 0.f);
+            bool done = (mat == 0) || emissive || (depth == PT_MAX_BOUNCE_COUNT - 1);
+            if (!done) done = !pt_shade_vertex(S, rng, mat, n, h.t, o, d, beta);
+            depth++;
+            if (done) {
+                alive = false;
+                if (isnan3(L) && retry + 1 < PT_MAX_NAN_RETRIES) {
+                    retry++;                                                // redraw this sample, main.cpp:1068
+                    n_nan++;
+                } else {
+                    if (isnan3(L)) L = f3(0, 0, 0);
+                    acc = acc + L;
+                    n_acc++;
+                    s += Sn;
+                    retry = 0;
+                }
+            }
+        }
+    }
+
+    // fixed-order tree sum over the S lanes of each pixel (deterministic for a given launch shape)
+    for (uint32_t off = Sn >> 1; off > 0; off >>= 1) {
+        acc.x += __shfl_xor_sync(0xffffffffu, acc.x, off);
+        acc.y += __shfl_xor_sync(0xffffffffu, acc.y, off);
+        acc.z += __shfl_xor_sync(0xffffffffu, acc.z, off);
+        n_acc += __shfl_xor_sync(0xffffffffu, n_acc, off);
+    }
+    if (active && sl == 0) {
+        float4 *p = A.accum + (size_t)y * A.width + x;
+        float4 v = *p;
+        v.x += acc.x; v.y += acc.y; v.z += acc.z; v.w += (float)n_acc;
+        *p = v;
+    }
+    // statistics: one atomic per warp
+    for (int off = 16; off > 0; off >>= 1) {
+        n_rays += __shfl_xor_sync(0xffffffffu, n_rays, off);
+        n_nan += __shfl_xor_sync(0xffffffffu, n_nan, off);
+    }
+    if (lane == 0 && A.counters) {
+        atomicAdd(A.counters + 0, (unsigned long long)n_rays);
+        if (n_nan) atomicAdd(A.counters + 1, (unsigned long long)n_nan);
+    }
+}
+
+// ---- resolve: mean -> ACES (e = 0.4) -> sRGB -> truncating BGRA pack (main.cpp:1172-1182) -------
+// Arithmetic kept in the reference's order with explicit round-to-nearest ops (no FMA contraction) and
+// powf evaluated in double, so that the bytes equal the CPU's for the same HDR input.
+__device__ __forceinline__ float pt_tonemap1(float x) {
+    float num = __fmul_rn(x, __fadd_rn(__fmul_rn(2.51f, x), 0.03f));
+    float den = __fadd_rn(0.4f, __fmul_rn(x, __fadd_rn(__fmul_rn(2.43f, x), 0.59f)));
+    float q = __fdiv_rn(num, den);
+    float m = (1.0f < q) ? 1.0f : q;            // std::min(v,1): NaN stays NaN ...
+    return (0.0f < m) ? m : 0.0f;               // ... std::max(0,NaN) = 0   (ray_math.hpp:298-304)
+}
+__device__ __forceinline__ float pt_linear_to_srgb(float Lc) {                // ray_math.hpp:320-332
+    if (Lc < 0.0f) Lc = 0.0f;
+    if (Lc > 1.0f) Lc = 1.0f;
+    float Sv = __fmul_rn(Lc, 12.92f);
+    if (Lc > 0.0031308f) {
+        float p = (float)pow((double)Lc, (double)(1.0f / 2.4f));
+        Sv = __fsub_rn(__fmul_rn(1.055f, p), 0.055f);
+    }
+    return Sv;
+}
+__device__ __forceinline__ uint32_t pt_resolve_pixel(float r, float g, float b) {
+    uint32_t R = (uint32_t)__fmul_rn(255.0f, pt_linear_to_srgb(pt_tonemap1(r)));
+    uint32_t G = (uint32_t)__fmul_rn(255.0f, pt_linear_to_srgb(pt_tonemap1(g)));
+    uint32_t B = (uint32_t)__fmul_rn(255.0f, pt_linear_to_srgb(pt_tonemap1(b)));
+    return (255u << 24) | (R << 16) | (G << 8) | B;                          // BGRAPack4x8, ray_math.hpp:196-202
+}
+
+__global__ void k_resolve(const float4 *__restrict__ accum, uint32_t *__restrict__ bgra, int n) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 a = accum[i];
+    float inv = a.w > 0.f ? __fdiv_rn(1.0f, a.w) : 0.f;
+    bgra[i] = pt_resolve_pixel(__fmul_rn(a.x, inv), __fmul_rn(a.y, inv), __fmul_rn(a.z, inv));
+}
+
+__global__ void k_resolve_colors(const float *__restrict__ rgb, uint32_t *__restrict__ out, uint32_t n) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    out[i] = pt_resolve_pixel(rgb[3 * i], rgb[3 * i + 1], rgb[3 * i + 2]);
+}
+
+// ---- parity / debug kernels ----------------------------------------------------------------------
+__device__ __forceinline__ void pt_store_hit(const PtDeviceScene &S, const PtHit &h, float3 o, float3 d, pt_hit *out) {
+    float3 n;
+    uint32_t mat;
+    pt_hit_surface(S, h, o, d, n, mat);
+    pt_hit r;
+    r.t = h.t;
+    r.kind = (h.id == PT_ID_MISS) ? PT_HIT_MISS : (int32_t)(h.id >> 28);
+    r.index = (h.id == PT_ID_MISS) ? -1 : (int32_t)(h.id & 0x0FFFFFFFu);
+    r.mat = mat;
+    r.normal.x = n.x; r.normal.y = n.y; r.normal.z = n.z;
+    *out = r;
+}
+
+__global__ void k_trace_rays(const __grid_constant__ PtDeviceScene S, const float *__restrict__ o, const float *__restrict__ d,
+                             pt_hit *__restrict__ out, uint32_t n) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float3 ro = f3(o[3 * i], o[3 * i + 1], o[3 * i + 2]), rd = f3(d[3 * i], d[3 * i + 1], d[3 * i + 2]);
+    PtHit h = pt_closest_hit(S, ro, rd);
+    pt_store_hit(S, h, ro, rd, out + i);
+}
+
+// jitter-free ray through the lower-left corner of each pixel, direction computed with IEEE
+// mul/add/sqrt/div in the reference's order so the ray itself is bit-identical to the CPU's
+__global__ void k_primary_hits(const __grid_constant__ PtDeviceScene S, int W, int H, pt_hit *__restrict__ out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= W * H) return;
+    int x = i % W, y = i / W;
+    const pt_camera &c = S.cam;
+    float fy = __fadd_rn(-1.0f, __fdiv_rn(__fmul_rn(2.0f, (float)y), (float)H));
+    float fx = __fadd_rn(-1.0f, __fdiv_rn(__fmul_rn(2.0f, (float)x), (float)W));
+    float sx = __fmul_rn(fx, c.half_film_w), sy = __fmul_rn(fy, c.half_film_h);
+    float px = __fadd_rn(__fadd_rn(c.frustum_center.x, __fmul_rn(sx, c.axis_x.x)), __fmul_rn(sy, c.axis_y.x));
+    float py = __fadd_rn(__fadd_rn(c.frustum_center.y, __fmul_rn(sx, c.axis_x.y)), __fmul_rn(sy, c.axis_y.y));
+    float pz = __fadd_rn(__fadd_rn(c.frustum_center.z, __fmul_rn(sx, c.axis_x.z)), __fmul_rn(sy, c.axis_y.z));
+    float dx = __fsub_rn(px, c.pos.x), dy = __fsub_rn(py, c.pos.y), dz = __fsub_rn(pz, c.pos.z);
+    float m = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)));
+    float3 rd = f3(__fdiv_rn(dx, m), __fdiv_rn(dy, m), __fdiv_rn(dz, m));
+    float3 ro = f3(c.pos);
+    PtHit h = pt_closest_hit(S, ro, rd);
+    pt_store_hit(S, h, ro, rd, out + i);
+}
+
+__global__ void k_trace_paths(const __grid_constant__ PtDeviceScene S, const float *__restrict__ o, const float *__restrict__ d,
+                              uint64_t seed, float *__restrict__ rgb, uint32_t n) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    PtRng rng;
+    rng.init(seed, i, 0u, 2u);
+    float3 L = pt_trace_path(S, rng, f3(o[3 * i], o[3 * i + 1], o[3 * i + 2]), f3(d[3 * i], d[3 * i + 1], d[3 * i + 2]));
+    rgb[3 * i] = L.x; rgb[3 * i + 1] = L.y; rgb[3 * i + 2] = L.z;
+}
+
+// ---- tile pack / unpack for the multi-GPU gather --------------------------------------------------
+// packed layout: own tile j (tile id = rank + j*count) occupies 1024 uint32 at offset j*1024, row-major
+// inside the tile, pixels outside the image zero
+__global__ void k_pack_tiles(const uint32_t *__restrict__ bgra, uint32_t *__restrict__ packed, int W, int H,
+                             uint32_t tiles_x, uint32_t rank, uint32_t count, uint32_t n_my_tiles) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_my_tiles * 1024u) return;
+    uint32_t j = i >> 10, p = i & 1023u;
+    uint32_t tile = rank + j * count;
+    int x = (int)((tile % tiles_x) * PT_TILE + (p & 31u)), y = (int)((tile / tiles_x) * PT_TILE + (p >> 5));
+    packed[i] = (x < W && y < H) ? bgra[(size_t)y * W + x] : 0u;
+}
+__global__ void k_unpack_tiles(uint32_t *__restrict__ bgra, const uint32_t *__restrict__ packed, int W, int H,
+                               uint32_t tiles_x, uint32_t rank, uint32_t count, uint32_t n_my_tiles) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_my_tiles * 1024u) return;
+    uint32_t j = i >> 10, p = i & 1023u;
+    uint32_t tile = rank + j * count;
+    int x = (int)((tile % tiles_x) * PT_TILE + (p & 31u)), y = (int)((tile / tiles_x) * PT_TILE + (p >> 5));
+    if (x < W && y < H) bgra[(size_t)y * W + x] = packed[i];
+}

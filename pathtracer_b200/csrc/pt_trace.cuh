@@ -1,0 +1,195 @@
+// Closest hit: the reference's RayCastIntersect (src/win32_main.cpp:406-556) re-organised for the GPU.
+// Analytic primitives come from short linear lists; triangles and small spheres from flattened BVH2s
+// with 64-byte nodes (4 x LDG.128) and 48-byte planar records (3 x LDG.128).  Nearest-hit semantics
+// are the reference's: accept t > 1e-4 (0.02 for quads), strict '<', and on an exact tie the primitive
+// the reference would have tested first (spheres, quads, planes, triangles, boxes; then lower index).
+#pragma once
+#include "pt_device.cuh"
+
+// RaySphereIntersect, main.cpp:2355-2379: near root only; sqrt(disc) must exceed 1e-9.  Returns t or -1.
+__device__ __forceinline__ float pt_sphere_t(float3 o, float3 d, float a, float4 s) {
+    float3 rel = f3(o.x - s.x, o.y - s.y, o.z - s.z);
+    float b = 2.0f * dot3(rel, d);
+    float c = dot3(rel, rel) - s.w * s.w;
+    float disc = b * b - 4.0f * a * c;
+    if (!(disc >= 0.f)) return -1.f;
+    float root = sqrtf(disc);
+    if (!(root > PT_TOLERANCE)) return -1.f;
+    float t = __fdividef(-b - root, 2.0f * a);
+    return (t > PT_MIN_HIT) ? t : -1.f;
+}
+
+// RayIntersectPlane, ray_math.hpp:334-341.  Returns t (any sign) or NaN when parallel.
+__device__ __forceinline__ float pt_plane_t(float3 o, float3 d, float4 p) {
+    float denom = dot3(p, d);
+    if (!((denom < -PT_TOLERANCE) || (denom > PT_TOLERANCE))) return __int_as_float(0x7fc00000);
+    return __fdividef(p.w - dot3(p, o), denom);
+}
+
+// RayIntersectPlanarShape<TRIANGLE|QUAD>, ray_math.hpp:357-381, on a precomputed PtPlanar record
+template <bool QUAD>
+__device__ __forceinline__ float pt_planar_t(float3 o, float3 d, const float4 r0, const float4 r1, const float4 r2, float min_hit) {
+    float t = pt_plane_t(o, d, r0);
+    if (!(t > min_hit)) return -1.f;
+    float3 P = f3(fmaf(t, d.x, o.x), fmaf(t, d.y, o.y), fmaf(t, d.z, o.z));
+    float alpha = dot3(r1, P) + r1.w;
+    float beta = dot3(r2, P) + r2.w;
+    bool in = QUAD ? (alpha >= 0.f && alpha <= 1.f && beta >= 0.f && beta <= 1.f)
+                   : (alpha >= 0.f && beta >= 0.f && (alpha + beta) <= 1.f);
+    return in ? t : -1.f;
+}
+
+// RayIntersectWithAABB2, ray_math.hpp:398-482: six faces in the order -z +z -x +x +y -y; the first face
+// with t >= 0 whose hit point lies inside the box wins.  Returns t or -1; *face = that face's index.
+__device__ __forceinline__ float pt_aabb_t(float3 o, float3 d, float4 mn, float4 mx, int *face) {
+#pragma unroll
+    for (int j = 0; j < 6; j++) {
+        float plane, oc, dc;
+        if (j < 2) { plane = (j == 0) ? mn.z : mx.z; oc = o.z; dc = d.z; }
+        else if (j < 4) { plane = (j == 2) ? mn.x : mx.x; oc = o.x; dc = d.x; }
+        else { plane = (j == 4) ? mx.y : mn.y; oc = o.y; dc = d.y; }
+        if (dc == 0.f) continue;
+        float t = (plane - oc) / dc;
+        if (t < 0.f) continue;
+        float x = (j == 2 || j == 3) ? plane : o.x + d.x * t;
+        float y = (j >= 4) ? plane : o.y + d.y * t;
+        float z = (j < 2) ? plane : o.z + d.z * t;
+        if (x >= mn.x && x <= mx.x && y >= mn.y && y <= mx.y && z >= mn.z && z <= mx.z) {
+            *face = j;
+            return t;
+        }
+    }
+    return -1.f;
+}
+
+__device__ __forceinline__ void pt_accept(PtHit &h, float t, uint32_t id) {
+    if (t < h.t || (t == h.t && id < h.id)) { h.t = t; h.id = id; }
+}
+
+enum { PT_LEAF_SPHERES = 0, PT_LEAF_TRIS = 1 };
+
+// Stack-based BVH2 walk, nearer child first, culled by the best t so far.
+template <int LEAF>
+__device__ __forceinline__ void pt_bvh_walk(const PtDeviceScene &S, const PtBvh &bvh, float3 o, float3 d, float a, PtHit &h) {
+    // reciprocal direction with zero components nudged so that no inf*0 appears in the slab test
+    float3 dd = f3(fabsf(d.x) < 1e-20f ? copysignf(1e-20f, d.x) : d.x,
+                   fabsf(d.y) < 1e-20f ? copysignf(1e-20f, d.y) : d.y,
+                   fabsf(d.z) < 1e-20f ? copysignf(1e-20f, d.z) : d.z);
+    float3 inv = f3(__frcp_rn(dd.x), __frcp_rn(dd.y), __frcp_rn(dd.z));
+    float3 ood = f3(o.x * inv.x, o.y * inv.y, o.z * inv.z);
+
+    int stack[PT_STACK_DEPTH];
+    int sp = 0;
+    int node = 0;
+    const float4 *nodes = reinterpret_cast<const float4 *>(bvh.nodes);
+    while (true) {
+        if (node >= 0) {
+            const float4 b0 = __ldg(nodes + 4 * node), b1 = __ldg(nodes + 4 * node + 1), b2 = __ldg(nodes + 4 * node + 2);
+            const int4 link = __ldg(reinterpret_cast<const int4 *>(nodes + 4 * node + 3));
+            // left child slabs
+            float lx0 = fmaf(b0.x, inv.x, -ood.x), lx1 = fmaf(b0.w, inv.x, -ood.x);
+            float ly0 = fmaf(b0.y, inv.y, -ood.y), ly1 = fmaf(b1.x, inv.y, -ood.y);
+            float lz0 = fmaf(b0.z, inv.z, -ood.z), lz1 = fmaf(b1.y, inv.z, -ood.z);
+            float ln = fmaxf(fmaxf(fminf(lx0, lx1), fminf(ly0, ly1)), fmaxf(fminf(lz0, lz1), 0.f));
+            float lf = fminf(fminf(fmaxf(lx0, lx1), fmaxf(ly0, ly1)), fminf(fmaxf(lz0, lz1), h.t)) * 1.0000004f;
+            // right child slabs
+            float rx0 = fmaf(b1.z, inv.x, -ood.x), rx1 = fmaf(b2.y, inv.x, -ood.x);
+            float ry0 = fmaf(b1.w, inv.y, -ood.y), ry1 = fmaf(b2.z, inv.y, -ood.y);
+            float rz0 = fmaf(b2.x, inv.z, -ood.z), rz1 = fmaf(b2.w, inv.z, -ood.z);
+            float rn = fmaxf(fmaxf(fminf(rx0, rx1), fminf(ry0, ry1)), fmaxf(fminf(rz0, rz1), 0.f));
+            float rf = fminf(fminf(fmaxf(rx0, rx1), fmaxf(ry0, ry1)), fminf(fmaxf(rz0, rz1), h.t)) * 1.0000004f;
+            bool hl = ln <= lf, hr = rn <= rf;
+            if (hl && hr) {
+                bool left_first = ln <= rn;
+                int nearc = left_first ? link.x : link.y;
+                int farc = left_first ? link.y : link.x;
+                stack[sp++] = farc;
+                node = nearc;
+                continue;
+            } else if (hl) { node = link.x; continue; }
+            else if (hr) { node = link.y; continue; }
+        } else {
+            uint32_t enc = (uint32_t)(~node);
+            uint32_t first = enc & 0xFFFFFFu, count = enc >> 24;
+            for (uint32_t i = 0; i < count; i++) {
+                uint32_t pos = first + i;
+                if (LEAF == PT_LEAF_TRIS) {
+                    const float4 *rec = reinterpret_cast<const float4 *>(S.tris + pos);
+                    float t = pt_planar_t<false>(o, d, __ldg(rec), __ldg(rec + 1), __ldg(rec + 2), PT_MIN_HIT);
+                    if (t > 0.f && t <= h.t) pt_accept(h, t, PT_ID(PT_HIT_TRIANGLE, __ldg(S.tri_ids + pos)));
+                } else {
+                    float t = pt_sphere_t(o, d, a, __ldg(S.bvh_spheres + pos));
+                    if (t > 0.f && t <= h.t) pt_accept(h, t, PT_ID(PT_HIT_SPHERE, __ldg(S.bvh_sphere_ids + pos)));
+                }
+            }
+        }
+        if (sp == 0) break;
+        node = stack[--sp];
+    }
+}
+
+// closest hit over the whole scene; h.id == PT_ID_MISS and h.t == FLT_MAX on a miss (main.cpp:411-412)
+__device__ __forceinline__ PtHit pt_closest_hit(const PtDeviceScene &S, float3 o, float3 d) {
+    PtHit h;
+    h.t = 3.402823466e+38f;
+    h.id = PT_ID_MISS;
+    const float a = dot3(d, d);
+    for (uint32_t i = 0; i < S.n_lin_spheres; i++) {
+        float t = pt_sphere_t(o, d, a, __ldg(S.lin_spheres + i));
+        if (t > 0.f && t <= h.t) pt_accept(h, t, PT_ID(PT_HIT_SPHERE, __ldg(S.lin_sphere_ids + i)));
+    }
+    for (uint32_t i = 0; i < S.n_quads; i++) {
+        const float4 *rec = reinterpret_cast<const float4 *>(S.quads + i);
+        float t = pt_planar_t<true>(o, d, __ldg(rec), __ldg(rec + 1), __ldg(rec + 2), PT_QUAD_MIN_HIT);
+        if (t > 0.f && t <= h.t) pt_accept(h, t, PT_ID(PT_HIT_QUAD, i));
+    }
+    for (uint32_t i = 0; i < S.n_planes; i++) {
+        float t = pt_plane_t(o, d, __ldg(S.planes + i));
+        if (t > PT_MIN_HIT && t <= h.t) pt_accept(h, t, PT_ID(PT_HIT_PLANE, i));
+    }
+    if (S.sphere_bvh.n_prims) pt_bvh_walk<PT_LEAF_SPHERES>(S, S.sphere_bvh, o, d, a, h);
+    if (S.tri_bvh.n_prims) pt_bvh_walk<PT_LEAF_TRIS>(S, S.tri_bvh, o, d, a, h);
+    for (uint32_t i = 0; i < S.n_aabbs; i++) {
+        int face;
+        float t = pt_aabb_t(o, d, __ldg(S.aabbs + 2 * i), __ldg(S.aabbs + 2 * i + 1), &face);
+        if (t > PT_MIN_HIT && t <= h.t) pt_accept(h, t, PT_ID(PT_HIT_AABB, i));
+    }
+    return h;
+}
+
+// geometric normal and material of a hit (ray_payload_t, include/ray.hpp:137-141)
+__device__ __forceinline__ void pt_hit_surface(const PtDeviceScene &S, const PtHit &h, float3 o, float3 d,
+                                               float3 &normal, uint32_t &mat) {
+    uint32_t kind = h.id >> 28, idx = h.id & 0x0FFFFFFFu;
+    if (h.id == PT_ID_MISS) { normal = f3(0, 0, 0); mat = 0; return; }
+    switch (kind) {
+        case PT_HIT_SPHERE: {
+            float4 s = __ldg(S.all_spheres + idx);
+            // Normalize(t*dir + (origin - centre)), main.cpp:2374
+            normal = normalize3(f3(fmaf(h.t, d.x, o.x - s.x), fmaf(h.t, d.y, o.y - s.y), fmaf(h.t, d.z, o.z - s.z)));
+            mat = __ldg(S.sphere_mat + idx);
+        } break;
+        case PT_HIT_QUAD: {
+            float4 r0 = __ldg(reinterpret_cast<const float4 *>(S.quads + idx));
+            normal = f3(r0.x, r0.y, r0.z);
+            mat = __ldg(S.quad_mat + idx);
+        } break;
+        case PT_HIT_PLANE: {
+            float4 p = __ldg(S.planes + idx);
+            normal = f3(p.x, p.y, p.z);
+            mat = __ldg(S.plane_mat + idx);
+        } break;
+        case PT_HIT_TRIANGLE: {
+            float4 n = __ldg(S.tri_normals + idx);
+            normal = f3(n.x, n.y, n.z);
+            mat = __ldg(S.tri_mat + idx);
+        } break;
+        default: {
+            int face = 0;
+            pt_aabb_t(o, d, __ldg(S.aabbs + 2 * idx), __ldg(S.aabbs + 2 * idx + 1), &face);
+            const float nx[6] = {0.f, 0.f, -1.f, 1.f, 0.f, 0.f}, ny[6] = {0.f, 0.f, 0.f, 0.f, 1.f, -1.f}, nz[6] = {-1.f, 1.f, 0.f, 0.f, 0.f, 0.f};
+            normal = f3(nx[face], ny[face], nz[face]);     // face normal table, main.cpp:540-543
+            mat = __ldg(S.aabb_mat + idx);
+        } break;
+    }
+}

@@ -1,0 +1,177 @@
+"""Python view of libpt_b200.so, the CUDA render core behind include/pt_api.h.
+
+This is the product path: pt_upload_scene / pt_render / pt_readback (+ the parity exports).  It
+never imports anything from oracle/ and has no CPU fallback: a missing library or a missing CUDA
+device raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import _ctypes_api as T
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libpt_b200.so")
+
+_lib = None
+
+
+class PtError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"pt error {code}: {msg}")
+        self.code = code
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(f"{LIB_PATH} is not built (python -c 'import __graft_entry__ as g; g.build()'); "
+                               "the render core has no CPU fallback")
+        L = C.CDLL(LIB_PATH)
+        L.pt_last_error.restype = C.c_char_p
+        L.pt_last_error.argtypes = [C.c_void_p]
+        L.pt_create.argtypes = [C.POINTER(T.Config), C.POINTER(C.c_void_p)]
+        L.pt_destroy.argtypes = [C.c_void_p]
+        L.pt_upload_scene.argtypes = [C.c_void_p, C.POINTER(T.Scene)]
+        L.pt_set_camera.argtypes = [C.c_void_p, C.POINTER(T.Camera)]
+        L.pt_render.argtypes = [C.c_void_p, C.POINTER(T.RenderParams)]
+        L.pt_synchronize.argtypes = [C.c_void_p]
+        L.pt_resolve.argtypes = [C.c_void_p]
+        L.pt_readback.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(T.Stats)]
+        L.pt_device_buffers.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
+                                        C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+        L.pt_set_stream.argtypes = [C.c_void_p, C.c_void_p]
+        L.pt_pack_tiles.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint32)]
+        L.pt_unpack_tiles.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]
+        L.pt_trace_rays.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.pt_primary_hits.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]
+        L.pt_trace_paths.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
+        L.pt_resolve_colors.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]
+        _lib = L
+    return _lib
+
+
+EXPORTS = ["pt_api_version", "pt_create", "pt_destroy", "pt_last_error", "pt_upload_scene", "pt_set_camera",
+           "pt_render", "pt_synchronize", "pt_resolve", "pt_readback", "pt_device_buffers", "pt_set_stream",
+           "pt_pack_tiles", "pt_unpack_tiles", "pt_trace_rays", "pt_primary_hits", "pt_trace_paths",
+           "pt_resolve_colors"]
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+class DeviceArray:
+    """Zero-copy handle on a device buffer owned by the context (for torch.as_tensor / NCCL)."""
+
+    def __init__(self, ptr, shape, typestr, owner):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False),
+                                         "version": 3, "strides": None}
+        self._owner = owner
+
+
+class RenderCore:
+    """One context on one GPU.  Not re-entrant; use from one host thread at a time."""
+
+    def __init__(self, device=0, bvh=T.BVH_HOST_SAH, kernel=T.KERNEL_AUTO, stream=None):
+        self._h = C.c_void_p()
+        cfg = T.Config(C.sizeof(T.Config), device, bvh, kernel, stream)
+        rc = lib().pt_create(C.byref(cfg), C.byref(self._h))
+        if rc != 0:
+            raise PtError(rc, lib().pt_last_error(None).decode())
+        self.width = self.height = 0
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise PtError(rc, lib().pt_last_error(self._h).decode())
+
+    def close(self):
+        if self._h:
+            lib().pt_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def upload_scene(self, scene):
+        self._ck(lib().pt_upload_scene(self._h, C.byref(scene)))
+
+    def set_camera(self, cam):
+        self._ck(lib().pt_set_camera(self._h, C.byref(cam)))
+
+    def set_stream(self, cuda_stream_ptr):
+        self._ck(lib().pt_set_stream(self._h, cuda_stream_ptr))
+
+    def render(self, width, height, pp, seed=1, sample_begin=0, sample_end=0, tile_rank=0, tile_count=1, clear=True):
+        p = T.RenderParams(C.sizeof(T.RenderParams), width, height, pp, seed, sample_begin, sample_end,
+                           tile_rank, tile_count, T.RENDER_CLEAR if clear else 0)
+        self._ck(lib().pt_render(self._h, C.byref(p)))
+        self.width, self.height = width, height
+
+    def synchronize(self):
+        self._ck(lib().pt_synchronize(self._h))
+
+    def resolve(self):
+        self._ck(lib().pt_resolve(self._h))
+
+    def readback(self, bgra=True, accum=False, out_bgra=None, out_accum=None):
+        """Returns (bgra [H,W] uint32 or None, accum [H,W,4] float32 or None, Stats)."""
+        b = a = None
+        if bgra:
+            b = out_bgra if out_bgra is not None else np.empty((self.height, self.width), np.uint32)
+        if accum:
+            a = out_accum if out_accum is not None else np.empty((self.height, self.width, 4), np.float32)
+        st = T.Stats()
+        self._ck(lib().pt_readback(self._h, _p(b), _p(a), C.byref(st)))
+        return b, a, st
+
+    def device_buffers(self):
+        pa, pb, w, h = C.c_void_p(), C.c_void_p(), C.c_int32(), C.c_int32()
+        self._ck(lib().pt_device_buffers(self._h, C.byref(pa), C.byref(pb), C.byref(w), C.byref(h)))
+        return (DeviceArray(pa.value, (h.value, w.value, 4), "<f4", self),
+                DeviceArray(pb.value, (h.value, w.value), "<u4", self))
+
+    def pack_tiles(self, dst_ptr, tile_rank, tile_count):
+        n = C.c_uint32()
+        self._ck(lib().pt_pack_tiles(self._h, dst_ptr, tile_rank, tile_count, C.byref(n)))
+        return n.value
+
+    def unpack_tiles(self, src_ptr, tile_rank, tile_count):
+        self._ck(lib().pt_unpack_tiles(self._h, src_ptr, tile_rank, tile_count))
+
+    # ---- parity / debug exports ----
+    def trace_rays(self, o, d):
+        o = np.ascontiguousarray(o, np.float32).reshape(-1, 3)
+        d = np.ascontiguousarray(d, np.float32).reshape(-1, 3)
+        hits = np.zeros(o.shape[0], T.HIT_DTYPE)
+        self._ck(lib().pt_trace_rays(self._h, o.shape[0], _p(o), _p(d), _p(hits)))
+        return hits
+
+    def primary_hits(self, width, height):
+        hits = np.zeros(width * height, T.HIT_DTYPE)
+        self._ck(lib().pt_primary_hits(self._h, width, height, _p(hits)))
+        return hits
+
+    def trace_paths(self, o, d, seed=1):
+        o = np.ascontiguousarray(o, np.float32).reshape(-1, 3)
+        d = np.ascontiguousarray(d, np.float32).reshape(-1, 3)
+        rgb = np.zeros((o.shape[0], 3), np.float32)
+        self._ck(lib().pt_trace_paths(self._h, o.shape[0], _p(o), _p(d), seed, _p(rgb)))
+        return rgb
+
+    def resolve_colors(self, rgb):
+        rgb = np.ascontiguousarray(rgb, np.float32).reshape(-1, 3)
+        out = np.zeros(rgb.shape[0], np.uint32)
+        self._ck(lib().pt_resolve_colors(self._h, rgb.shape[0], _p(rgb), _p(out)))
+        return out
+
+
+def tile_ids(width, height, tile_rank, tile_count):
+    """Row-major ids of the 32x32 tiles (src/win32_main.cpp:888-904) owned by tile_rank."""
+    tx, ty = (width + 31) // 32, (height + 31) // 32
+    return list(range(tile_rank, tx * ty, tile_count))
