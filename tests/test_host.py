@@ -1,0 +1,156 @@
+"""Host library (libpt_host.so) against the reference's own scene dumps, BMP bytes and CLI behaviour."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, golden
+from pathtracer_b200 import _ctypes_api as T
+from pathtracer_b200 import host
+
+
+@pytest.mark.parametrize("w", [1, 2, 3, 4, 5])
+def test_world_equals_reference_dump(worlds, w):
+    """Byte-for-byte: materials, spheres, planes, quads, triangles and the derived camera (160x90)."""
+    g = golden(f"scene_w{w}.npz")
+    s = host.scene_arrays(worlds(w).scene(160, 90))
+    for k in ["materials", "spheres", "planes", "quads", "aabbs"]:
+        assert s[k].tobytes() == g[k].tobytes(), k
+    assert np.array_equal(s["tri_points"], g["tri_points"])
+    assert np.array_equal(s["tri_materials"], g["tri_materials"])
+    assert s["camera"].tobytes() == g["camera"].tobytes()
+
+
+def test_world_counts(worlds):
+    n = {w: host.scene_arrays(worlds(w).scene(64, 36)) for w in range(1, 6)}
+    assert len(n[1]["spheres"]) == 5 and len(n[1]["materials"]) == 6 and all(t is not None for t in n[1]["textures"])
+    assert len(n[2]["spheres"]) == 122 and len(n[2]["planes"]) == 1 and len(n[2]["materials"]) == 124
+    assert len(n[3]["spheres"]) == 1 and len(n[3]["quads"]) == 5 and len(n[3]["materials"]) == 5
+    assert len(n[4]["spheres"]) == 484 and n[4]["flags"] & T.SCENE_JUST_COSINE and n[4]["camera"]["use_pinhole"] == 0
+    assert len(n[5]["tri_materials"]) == 752 and len(n[5]["materials"]) == 9
+
+
+def test_world4_layout_depends_on_scene_seed():
+    a = host.scene_arrays(host.HostWorld(4, scene_seed=7).scene(64, 36))
+    b = host.scene_arrays(host.HostWorld(4, scene_seed=8).scene(64, 36))
+    assert a["spheres"].tobytes() != b["spheres"].tobytes()
+    # "roughness = 1 - material.metalness" reads the PREVIOUS material (main.cpp:1994)
+    m = a["materials"]
+    metal = np.nonzero(m["metalness"][2:-2] > 0)[0] + 2
+    assert all(np.float32(1.0) - m["metalness"][i - 1] == m["roughness"][i] for i in metal)
+
+
+def test_lens_flag_and_texture_flags(worlds):
+    s = worlds(5).scene(64, 36, lens=True, tex_flags=T.SCENE_NORMAL_MAPS)
+    assert s.camera.use_pinhole == 0 and s.flags == T.SCENE_NORMAL_MAPS
+    # thin lens focal length 1/(1/0.098 - 1/focalDistance), main.cpp:2206-2207
+    assert np.float32(s.camera.focal_length) == np.float32(1.0) / (np.float32(1.0) / np.float32(0.098) - np.float32(1.0) / np.float32(5.0))
+
+
+def test_camera_portrait_aspect(worlds):
+    s = host.scene_arrays(worlds(3).scene(90, 160))
+    c = s["camera"]
+    assert c["film_w"] < c["film_h"] and np.float32(c["half_pixel_w"]) == np.float32(1.0) / np.float32(90)
+
+
+def test_bmp_bytes_equal_reference(tmp_path):
+    g = golden("common.npz")
+    p = tmp_path / "out.bmp"
+    host.write_bmp(str(p), g["bmp_pixels"])
+    got = np.fromfile(p, np.uint8)
+    assert got.tobytes() == g["bmp_bytes"].tobytes()
+    assert len(got) == 58 + 64 * 36 * 4
+    back = host.read_bmp(str(p))
+    assert np.array_equal(back, g["bmp_pixels"])
+
+
+def test_png_decoder_matches_pil():
+    from PIL import Image
+    path = os.path.join(ROOT, "res", "rusty-metal_roughness.png")
+    mine = host.load_png(path)
+    ref = np.asarray(Image.open(path).convert("RGBA"))
+    assert np.array_equal(mine, ref)
+
+
+def test_png_decoder_filters_and_types(tmp_path):
+    from PIL import Image
+    rng = np.random.default_rng(0)
+    for mode, shape in [("L", (37, 53)), ("RGB", (37, 53, 3)), ("RGBA", (37, 53, 4)), ("LA", (37, 53, 2))]:
+        # smooth + noisy content so that PIL picks different scanline filters
+        a = (rng.random(shape) * 40 + np.linspace(0, 200, shape[1]).reshape(1, -1, *([1] * (len(shape) - 2)))).astype(np.uint8)
+        p = tmp_path / f"{mode}.png"
+        Image.fromarray(a, mode).save(p)
+        assert np.array_equal(host.load_png(str(p)), np.asarray(Image.open(p).convert("RGBA"))), mode
+    pal = Image.fromarray((rng.random((20, 31)) * 255).astype(np.uint8), "L").convert("P")
+    p = tmp_path / "pal.png"
+    pal.save(p)
+    assert np.array_equal(host.load_png(str(p)), np.asarray(Image.open(p).convert("RGBA")))
+
+
+def test_png_errors(tmp_path):
+    p = tmp_path / "bad.png"
+    p.write_bytes(b"not a png at all")
+    with pytest.raises(RuntimeError):
+        host.load_png(str(p))
+    with pytest.raises(RuntimeError):
+        host.load_png(str(tmp_path / "missing.png"))
+
+
+def test_glb_import_semantics(worlds):
+    s = host.scene_arrays(worlds(5).scene(64, 36))
+    # one material per primitive from baseColorFactor; the first (no factor) defaults to white
+    assert np.allclose(s["materials"]["albedo"][3], [1, 1, 1])
+    assert np.allclose(s["materials"]["albedo"][4], [1, 0, 0])
+    assert set(np.unique(s["tri_materials"])) == {3, 4, 5, 6, 7, 8}
+    assert (s["materials"]["roughness"][3:] == 1).all() and (s["materials"]["metalness"][3:] == 0).all()
+    pts = s["tri_points"].reshape(-1, 3)
+    assert np.allclose(pts.min(0), [-1.125, -0.650, -0.013], atol=2e-3) and np.allclose(pts.max(0), [1.235, 0.570, 2.341], atol=2e-3)
+
+
+def test_missing_assets_fail_loudly(tmp_path):
+    with pytest.raises(RuntimeError):
+        host.HostWorld(5, res_dir=str(tmp_path))
+    with pytest.raises(RuntimeError):
+        host.HostWorld(9)
+
+
+def _parse(args, capfd):
+    rc, o = host.parse_args(["pathtracer"] + args)
+    out = capfd.readouterr().out
+    return rc, o, out
+
+
+def test_args_defaults(capfd):
+    rc, o, out = _parse([], capfd)
+    assert rc == 0 and o.pp == 4 and o.world == 1 and o.lens == 0 and o.normals == o.metalness == o.roughness == 1
+    assert o.width == 1280 and o.height == 720 and o.out_path == b"test.bmp"
+    assert re.search(r"System has \d+ core\(s\)\.\nUsing \d+ thread\(s\)\.\n\n", out)
+
+
+def test_args_reference_quirks(capfd):
+    # digits after t/p/w are NOT consumed: each prints the reference's warning (main.cpp:2187-2189)
+    rc, o, out = _parse(["-w5", "-p16", "-nmr", "-d"], capfd)
+    assert o.world == 5 and o.pp == 16 and o.lens == 1 and o.normals == o.metalness == o.roughness == 0
+    assert out.count("Warning: invalid program arugment -5") == 1
+    assert out.count("Warning: invalid program arugment -1") == 1 and out.count("Warning: invalid program arugment -6") == 1
+    rc, o, out = _parse(["-p5000", "-w9", "-t100000"], capfd)
+    assert o.pp == 1000 and o.world == 5 and o.threads == o.system_cores
+    rc, o, out = _parse(["-w0", "-p-3"], capfd)
+    assert o.world == 1 and o.pp == 0
+    rc, o, out = _parse(["notaflag", "-x"], capfd)
+    assert "Warning: invalid program arugment -x" in out
+
+
+def test_args_long_options(capfd):
+    rc, o, out = _parse(["--width", "1920", "--height=1080", "--gpus", "8", "--shard", "samples", "--seed", "42",
+                         "--scene-seed=9", "--out", "a.bmp", "-w3"], capfd)
+    assert (o.width, o.height, o.gpus, o.shard_samples, o.seed, o.scene_seed, o.world) == (1920, 1080, 8, 1, 42, 9, 3)
+    assert o.out_path == b"a.bmp"
+    assert out.count("Warning") == 1 and "Warning: invalid program arugment -3" in out   # only -w3's digit
+
+
+def test_args_help(capfd):
+    rc, o, out = _parse(["-h"], capfd)
+    assert rc == 1 and out.startswith("usage: Pathtracer.exe [options]\n") and "\tw<int>" in out and "5:\tMario N64 model." in out
