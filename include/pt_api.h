@@ -210,6 +210,10 @@ int pt_trace_paths(pt_context *ctx, uint32_t n, const float *origins, const floa
 /* resolve n HDR colours (n*3 floats, host) to BGRA8 exactly as pt_resolve does */
 int pt_resolve_colors(pt_context *ctx, uint32_t n, const float *rgb, uint32_t *bgra_out);
 
+/* measurement helper for the roofline: achieved FP32 FMA throughput of this device (TFLOP/s, best of 5
+   runs of an 8-way-ILP FMA chain on every SM), timed with CUDA events on the context's stream */
+int pt_measure_fp32_peak(pt_context *ctx, float *tflops_out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -576,3 +576,33 @@ extern "C" int pt_resolve_colors(pt_context *ctx, uint32_t n, const float *rgb, 
     CK(cudaStreamSynchronize(ctx->stream));
     return PT_OK;
 }
+
+extern "C" int pt_measure_fp32_peak(pt_context *ctx, float *tflops_out) {
+    if (!ctx || !tflops_out) return PT_ERR_INVALID_ARG;
+    CK(cudaSetDevice(ctx->device));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, ctx->device));
+    const int blocks = prop.multiProcessorCount * 8, threads = 256, iters = 4096;
+    ScopedDev sd;
+    float *out = (float *)sd.alloc((size_t)blocks * threads * sizeof(float));
+    if (!out) return fail(ctx, PT_ERR_OOM, "pt_measure_fp32_peak: cudaMalloc failed");
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0));
+    CK(cudaEventCreate(&e1));
+    float best = 0.f;
+    for (int run = 0; run < 6; run++) {
+        CK(cudaEventRecord(e0, ctx->stream));
+        k_fma_peak<<<blocks, threads, 0, ctx->stream>>>(out, iters);
+        CK(cudaEventRecord(e1, ctx->stream));
+        CK(cudaEventSynchronize(e1));
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, e0, e1));
+        double flops = (double)blocks * threads * (double)iters * 64.0 * 2.0;
+        float tf = (float)(flops / (ms * 1e-3) * 1e-12);
+        if (run > 0 && tf > best) best = tf;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *tflops_out = best;
+    return PT_OK;
+}

@@ -276,3 +276,22 @@ __global__ void k_unpack_tiles(uint32_t *__restrict__ bgra, const uint32_t *__re
     int x = (int)((tile % tiles_x) * PT_TILE + (p & 31u)), y = (int)((tile / tiles_x) * PT_TILE + (p >> 5));
     if (x < W && y < H) bgra[(size_t)y * W + x] = packed[i];
 }
+
+// ---- FP32 roofline probe: 8 independent FMA chains per thread ------------------------------------------
+__global__ void k_fma_peak(float *out, int iters) {
+    float a[8];
+    const float b = 1.0000001f, c = 1e-7f;
+#pragma unroll
+    for (int k = 0; k < 8; k++) a[k] = (float)(threadIdx.x + k) * 1e-3f;
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int r = 0; r < 8; r++) {
+#pragma unroll
+            for (int k = 0; k < 8; k++) a[k] = fmaf(a[k], b, c);
+        }
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; k++) s += a[k];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}

@@ -1,0 +1,143 @@
+"""Sharding one frame over the GPUs of a box: one process per GPU, torch.distributed for the plumbing.
+
+The reference's only parallelism is CPU threads over 32x32 tiles handed out by MasterThread
+(src/win32_main.cpp:888-960).  Two partitions of the same work, both with exactly one exchange:
+
+  * "tiles"   rank r renders the tiles t with t % G == r (interleaved, so sky tiles and Mario tiles
+              spread evenly), resolves them, packs them tile-major and the packs are GATHERED to
+              rank 0 (4 B/pixel in total, no reduction).  Counter-based RNG keyed by (pixel, sample)
+              => the frame is bit-identical for any G.
+  * "samples" rank r renders samples [r*spp/G, (r+1)*spp/G) of every pixel into its float4
+              accumulation buffer; one REDUCE(sum, fp32) to rank 0, which resolves.
+
+The collectives run on torch tensors, so the same code runs on NCCL (GPU) and on gloo (CPU tests,
+where the render step is injected).  Nothing here does render arithmetic.
+"""
+import numpy as np
+
+TILE = 32
+
+
+def tile_grid(width, height):
+    return (width + TILE - 1) // TILE, (height + TILE - 1) // TILE
+
+
+def my_tiles(width, height, rank, world):
+    tx, ty = tile_grid(width, height)
+    return list(range(rank, tx * ty, world))
+
+
+def max_tiles_per_rank(width, height, world):
+    tx, ty = tile_grid(width, height)
+    return (tx * ty + world - 1) // world
+
+
+def sample_range(pp, rank, world):
+    """Contiguous slice of the pp*pp sample list owned by `rank` (sizes differ by at most one)."""
+    spp = pp * pp
+    base, extra = divmod(spp, world)
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+def pack_tiles_host(bgra, rank, world):
+    """numpy mirror of k_pack_tiles (csrc/pt_kernels.cuh): [n_tiles, 32, 32] uint32, zero padded."""
+    h, w = bgra.shape
+    tx, _ = tile_grid(w, h)
+    ids = my_tiles(w, h, rank, world)
+    out = np.zeros((len(ids), TILE, TILE), np.uint32)
+    for j, t in enumerate(ids):
+        x0, y0 = (t % tx) * TILE, (t // tx) * TILE
+        blk = bgra[y0:y0 + TILE, x0:x0 + TILE]
+        out[j, :blk.shape[0], :blk.shape[1]] = blk
+    return out
+
+
+def unpack_tiles_host(bgra, packed, rank, world):
+    """numpy mirror of k_unpack_tiles."""
+    h, w = bgra.shape
+    tx, _ = tile_grid(w, h)
+    for j, t in enumerate(my_tiles(w, h, rank, world)):
+        x0, y0 = (t % tx) * TILE, (t // tx) * TILE
+        hh, ww = min(TILE, h - y0), min(TILE, w - x0)
+        bgra[y0:y0 + hh, x0:x0 + ww] = packed[j, :hh, :ww]
+    return bgra
+
+
+def gather_packed_tiles(packed, width, height, group=None):
+    """Gather every rank's packed tiles ([n_r*1024] int32 tensor) to rank 0.
+    Returns the list of per-rank tensors on rank 0 (padded to the same length), else None."""
+    import torch
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    n_max = max_tiles_per_rank(width, height, world) * TILE * TILE
+    if packed.numel() < n_max:
+        packed = torch.cat([packed, packed.new_zeros(n_max - packed.numel())])
+    if world == 1:
+        return [packed]
+    bufs = [torch.empty_like(packed) for _ in range(world)] if rank == 0 else None
+    dist.gather(packed, bufs, dst=0, group=group)
+    return bufs
+
+
+def reduce_accum(accum, group=None):
+    """Sum the ranks' float accumulation buffers into rank 0's (in place)."""
+    import torch.distributed as dist
+    if dist.get_world_size(group) > 1:
+        dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM, group=group)
+    return accum
+
+
+class ShardedFrame:
+    """Render one frame on this rank's GPU and exchange it; `core` is a render.RenderCore whose
+    stream is torch's current stream (so the collectives order after the kernels)."""
+
+    def __init__(self, core, width, height, mode="tiles", group=None):
+        import torch
+        import torch.distributed as dist
+        self.core, self.w, self.h, self.mode, self.group = core, width, height, mode, group
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.torch = torch
+        self._packed = None
+        self.launches = 0
+
+    def render(self, pp, seed):
+        """Returns rank 0's resolved BGRA frame as a device int32 tensor [H, W] (None on other ranks)."""
+        torch, core = self.torch, self.core
+        self.launches = 0
+        if self.mode == "tiles":
+            core.render(self.w, self.h, pp, seed=seed, tile_rank=self.rank, tile_count=self.world)
+            core.resolve()
+            self.launches += 2
+            if self.world == 1:
+                _, b = core.device_buffers()
+                return torch.as_tensor(b, device="cuda")
+            n_max = max_tiles_per_rank(self.w, self.h, self.world) * TILE * TILE
+            if self._packed is None:
+                self._packed = torch.zeros(n_max, dtype=torch.int32, device="cuda")
+            core.pack_tiles(self._packed.data_ptr(), self.rank, self.world)
+            self.launches += 1
+            bufs = gather_packed_tiles(self._packed, self.w, self.h, self.group)
+            if self.rank != 0:
+                return None
+            for r in range(1, self.world):
+                core.unpack_tiles(bufs[r].data_ptr(), r, self.world)
+                self.launches += 1
+            _, b = core.device_buffers()
+            return torch.as_tensor(b, device="cuda")
+        lo, hi = sample_range(pp, self.rank, self.world)
+        if hi > lo:
+            core.render(self.w, self.h, pp, seed=seed, sample_begin=lo, sample_end=hi)
+        else:
+            core.render(self.w, self.h, 0, seed=seed)      # more ranks than samples: contribute zeros
+        self.launches += 1
+        a, b = core.device_buffers()
+        acc = torch.as_tensor(a, device="cuda")
+        reduce_accum(acc, self.group)
+        if self.rank != 0:
+            return None
+        core.resolve()
+        self.launches += 1
+        return torch.as_tensor(b, device="cuda")

@@ -49,6 +49,7 @@ def lib():
         L.pt_primary_hits.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]
         L.pt_trace_paths.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
         L.pt_resolve_colors.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]
+        L.pt_measure_fp32_peak.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
         _lib = L
     return _lib
 
@@ -56,7 +57,7 @@ def lib():
 EXPORTS = ["pt_api_version", "pt_create", "pt_destroy", "pt_last_error", "pt_upload_scene", "pt_set_camera",
            "pt_render", "pt_synchronize", "pt_resolve", "pt_readback", "pt_device_buffers", "pt_set_stream",
            "pt_pack_tiles", "pt_unpack_tiles", "pt_trace_rays", "pt_primary_hits", "pt_trace_paths",
-           "pt_resolve_colors"]
+           "pt_resolve_colors", "pt_measure_fp32_peak"]
 
 
 def _p(a):
@@ -134,7 +135,7 @@ class RenderCore:
         pa, pb, w, h = C.c_void_p(), C.c_void_p(), C.c_int32(), C.c_int32()
         self._ck(lib().pt_device_buffers(self._h, C.byref(pa), C.byref(pb), C.byref(w), C.byref(h)))
         return (DeviceArray(pa.value, (h.value, w.value, 4), "<f4", self),
-                DeviceArray(pb.value, (h.value, w.value), "<u4", self))
+                DeviceArray(pb.value, (h.value, w.value), "<i4", self))   # BGRA words viewed as int32 for torch
 
     def pack_tiles(self, dst_ptr, tile_rank, tile_count):
         n = C.c_uint32()
@@ -169,6 +170,12 @@ class RenderCore:
         out = np.zeros(rgb.shape[0], np.uint32)
         self._ck(lib().pt_resolve_colors(self._h, rgb.shape[0], _p(rgb), _p(out)))
         return out
+
+
+    def measure_fp32_peak(self):
+        v = C.c_float()
+        self._ck(lib().pt_measure_fp32_peak(self._h, C.byref(v)))
+        return v.value
 
 
 def tile_ids(width, height, tile_rank, tile_count):

@@ -1,0 +1,218 @@
+"""Size-independent properties of the CUDA path (checked up to BASELINE.json's full sizes), edge cases
+and the error behaviour of the C-ABI."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from oracle import pt_oracle as O
+from pathtracer_b200 import _ctypes_api as T
+from pathtracer_b200 import render
+
+pytestmark = pytest.mark.gpu
+
+
+def _frame(core, W, H, pp, **kw):
+    core.render(W, H, pp, **kw)
+    b, a, st = core.readback(True, True)
+    return b.copy(), a.copy(), st
+
+
+def test_deterministic_and_seed_dependent(core, worlds):
+    core.upload_scene(worlds(5).scene(200, 120))
+    b1, a1, _ = _frame(core, 200, 120, 4, seed=3)
+    b2, a2, _ = _frame(core, 200, 120, 4, seed=3)
+    b3, a3, _ = _frame(core, 200, 120, 4, seed=4)
+    assert np.array_equal(a1, a2) and np.array_equal(b1, b2)
+    assert not np.array_equal(a1, a3)
+
+
+@pytest.mark.parametrize("G", [2, 3, 8])
+def test_tile_sharding_is_bit_identical(core, worlds, G):
+    """Counter RNG keyed by (pixel, sample): the union of the ranks' tiles equals the 1-GPU frame, bit for bit."""
+    W, H, pp = 300, 170, 4          # not multiples of 32: clipped edge tiles
+    core.upload_scene(worlds(5).scene(W, H))
+    full_b, full_a, _ = _frame(core, W, H, pp, seed=5)
+    acc = np.zeros_like(full_a)
+    covered = np.zeros((H, W), np.int32)
+    for r in range(G):
+        b, a, st = _frame(core, W, H, pp, seed=5, tile_rank=r, tile_count=G)
+        mine = a[..., 3] > 0
+        covered += mine
+        acc[mine] = a[mine]
+        for t in render.tile_ids(W, H, r, G):
+            tx, ty = (t % ((W + 31) // 32)) * 32, (t // ((W + 31) // 32)) * 32
+            assert mine[ty:ty + 32, tx:tx + 32].all()
+        assert st.samples == mine.sum() * pp * pp
+    assert (covered == 1).all()
+    assert np.array_equal(acc, full_a)
+
+
+def test_tile_pack_unpack_roundtrip(core, worlds):
+    import torch
+    W, H, pp, G = 300, 170, 2, 3
+    core.upload_scene(worlds(3).scene(W, H))
+    full_b, _, _ = _frame(core, W, H, pp, seed=5)
+    packs = []
+    for r in range(G):
+        _frame(core, W, H, pp, seed=5, tile_rank=r, tile_count=G)
+        n = len(render.tile_ids(W, H, r, G))
+        buf = torch.zeros(n * 1024, dtype=torch.int32, device="cuda")
+        assert core.pack_tiles(buf.data_ptr(), r, G) == n
+        core.synchronize()
+        packs.append(buf)
+    _frame(core, W, H, 0, seed=5)          # clears accum; bgra of a zero-sample frame
+    for r in range(G):
+        core.unpack_tiles(packs[r].data_ptr(), r, G)
+    core.synchronize()
+    _, bdev = core.device_buffers()
+    got = torch.as_tensor(bdev, device="cuda").cpu().numpy().view(np.uint32).reshape(H, W)
+    assert np.array_equal(got, full_b)
+
+
+def test_sample_sharding_sums_to_full_frame(core, worlds):
+    W, H, pp = 160, 90, 6
+    core.upload_scene(worlds(3).scene(W, H))
+    _, full, _ = _frame(core, W, H, pp, seed=8)
+    parts = np.zeros_like(full, dtype=np.float64)
+    bounds = [0, 9, 18, 27, 36]
+    for lo, hi in zip(bounds[:-1], bounds[1:]):
+        _, a, st = _frame(core, W, H, pp, seed=8, sample_begin=lo, sample_end=hi)
+        assert (a[..., 3] == hi - lo).all() and st.samples == W * H * (hi - lo)
+        parts += a
+    assert (parts[..., 3] == pp * pp).all()
+    assert np.allclose(parts[..., :3], full[..., :3], rtol=2e-5, atol=1e-5)
+    # accumulate-without-clear gives the same as the sum
+    core.render(W, H, pp, seed=8, sample_begin=0, sample_end=18, clear=True)
+    core.render(W, H, pp, seed=8, sample_begin=18, sample_end=36, clear=False)
+    _, a2, st = core.readback(False, True)
+    assert st.samples == W * H * 36 and np.allclose(a2[..., :3], full[..., :3], rtol=2e-5, atol=1e-5)
+
+
+@pytest.mark.parametrize("lanes", [0, 1, 3, 5])
+def test_launch_shape_does_not_change_the_samples(worlds, lanes, monkeypatch):
+    """S sample-lanes x P pixels per warp is a scheduling choice only: the per-pixel sums agree up to
+    float summation order and the sample counts are identical."""
+    W, H, pp = 100, 70, 6
+    monkeypatch.setenv("PT_SAMPLE_LANES_LOG2", str(lanes))
+    rc = render.RenderCore(0)
+    rc.upload_scene(worlds(5).scene(W, H))
+    rc.render(W, H, pp, seed=2)
+    _, a, _ = rc.readback(False, True)
+    monkeypatch.delenv("PT_SAMPLE_LANES_LOG2")
+    rc2 = render.RenderCore(0)
+    rc2.upload_scene(worlds(5).scene(W, H))
+    rc2.render(W, H, pp, seed=2)
+    _, b, _ = rc2.readback(False, True)
+    assert np.array_equal(a[..., 3], b[..., 3])
+    assert np.allclose(a[..., :3], b[..., :3], rtol=1e-5, atol=1e-5)
+    rc.close(); rc2.close()
+
+
+@pytest.mark.parametrize("W,H,pp", [(1, 1, 3), (33, 31, 1), (31, 65, 2), (64, 64, 5)])
+def test_ragged_sizes_vs_oracle(core, worlds, W, H, pp):
+    sc = worlds(3).scene(W, H)
+    core.upload_scene(sc)
+    b, a, st = _frame(core, W, H, pp, seed=1)
+    assert a.shape == (H, W, 4) and (a[..., 3] == pp * pp).all()
+    orc = O.render(sc, W, H, pp, O.RNG_PHILOX, 1)
+    om = orc["sum"] / (pp * pp)
+    gm = a[..., :3] / (pp * pp)
+    rel = np.abs(gm - om).max(2) / np.maximum(1e-2, np.abs(om).max(2))
+    assert (rel < 2e-3).mean() >= 0.97
+
+
+def test_zero_samples_frame(core, worlds):
+    """-p0 is legal in the reference (clamp to [0,1000], main.cpp:2171): no samples, colour 0 -> black, A=255."""
+    core.upload_scene(worlds(2).scene(40, 30))
+    b, a, st = _frame(core, 40, 30, 0)
+    assert (a == 0).all() and st.samples == 0 and (b == 0xFF000000).all()
+
+
+def test_max_pp_is_accepted_and_more_is_rejected(core, worlds):
+    core.upload_scene(worlds(3).scene(2, 2))
+    b, a, st = _frame(core, 2, 2, 1000, sample_begin=0, sample_end=64)     # RAYS_PER_PIXEL_MAX, main.cpp:89
+    assert (a[..., 3] == 64).all()
+    with pytest.raises(render.PtError):
+        core.render(2, 2, 1001)
+
+
+def test_empty_primitive_lists(core):
+    """A world with nothing but the sky and the (required) light sphere far away: every ray misses."""
+    from pathtracer_b200 import host
+    mats = (T.Material * 2)()
+    for m in mats:
+        m.alpha, m.ior, m.roughness = 1, 1, 1
+    mats[0].emit = T.V3(0.25, 0.5, 0.75)
+    mats[1].emit = T.V3(15, 15, 15)
+    sph = (T.Sphere * 1)(T.Sphere(T.V3(0, -5000, 0), 1.0, 1))
+    s = T.Scene()
+    s.struct_size = C.sizeof(T.Scene)
+    s.n_materials, s.materials = 2, C.cast(mats, C.c_void_p)
+    s.n_spheres, s.spheres = 1, C.cast(sph, C.c_void_p)
+    s.camera.use_pinhole = 1
+    s.camera.pos, s.camera.target, s.camera.fov = T.V3(0, -10, 1), T.V3(0, 0, 0), 45.0
+    s.camera.focal_distance, s.camera.aperture_radius = 5.0, 0.035
+    host.define_camera(s.camera, 32, 16)
+    core.upload_scene(s)
+    h = core.primary_hits(32, 16)
+    assert (h["kind"] == 0).all() and (h["index"] == -1).all()
+    b, a, _ = _frame(core, 32, 16, 2)
+    assert np.allclose(a[..., :3] / 4, [0.25, 0.5, 0.75])
+    assert (b == O.resolve(np.array([[0.25, 0.5, 0.75]], np.float32))[0]).all()
+
+
+def test_error_codes(core, worlds):
+    L = render.lib()
+    sc = worlds(3).scene(16, 16)
+    bad = T.Scene.from_buffer_copy(sc)
+    bad.struct_size = 4
+    assert L.pt_upload_scene(core._h, C.byref(bad)) == -1 and b"struct_size" in L.pt_last_error(core._h)
+    bad = T.Scene.from_buffer_copy(sc)
+    bad.n_materials = 0
+    assert L.pt_upload_scene(core._h, C.byref(bad)) == -1
+    sph = np.frombuffer((C.c_uint8 * (sc.n_spheres * 20)).from_address(sc.spheres), T.SPHERE_DTYPE).copy()
+    sph["mat"][0] = 999
+    bad = T.Scene.from_buffer_copy(sc)
+    bad.spheres = sph.ctypes.data
+    assert L.pt_upload_scene(core._h, C.byref(bad)) == -1 and b"material" in L.pt_last_error(core._h)
+    fresh = render.RenderCore(0)
+    with pytest.raises(render.PtError) as e:
+        fresh.render(16, 16, 2)
+    assert e.value.code == -4
+    p = T.RenderParams(C.sizeof(T.RenderParams), 16, 16, 2, 1, 0, 0, 0, 1, 1)
+    assert L.pt_readback(fresh._h, None, None, None) == -5
+    fresh.upload_scene(sc)
+    p.tile_rank, p.tile_count = 3, 2
+    assert L.pt_render(fresh._h, C.byref(p)) == -1
+    p.tile_rank, p.tile_count, p.sample_begin, p.sample_end = 0, 1, 3, 2
+    assert L.pt_render(fresh._h, C.byref(p)) == -1
+    p.sample_begin, p.sample_end, p.width = 0, 0, -5
+    assert L.pt_render(fresh._h, C.byref(p)) == -1
+    cfg = T.Config(C.sizeof(T.Config), 4096, 0, 0, None)
+    h = C.c_void_p()
+    assert L.pt_create(C.byref(cfg), C.byref(h)) == -1
+    fresh.close()
+
+
+def test_headline_config_properties(core, worlds):
+    """w5 1920x1080 -p32 (the metric's configuration): sample counts, energy vs a low-spp oracle strip,
+    tile sharding at full size bit-identical on a strip, no NaN in the accumulation buffer."""
+    W, H, pp = 1920, 1080, 32
+    sc = worlds(5).scene(W, H)
+    core.upload_scene(sc)
+    b, a, st = _frame(core, W, H, pp, seed=1)
+    assert st.samples == W * H * pp * pp and (a[..., 3] == pp * pp).all()
+    assert np.isfinite(a).all()
+    assert 1.35 < st.rays / st.samples < 1.50          # the reference measures 1.418 rays per sample
+    mean = a[..., :3] / (pp * pp)
+    # a 64x4 strip through Mario against the oracle at 64 spp (different sample count -> statistical)
+    x0, y0 = 930, 500
+    orc = O.render(sc, W, H, 8, O.RNG_PHILOX, 77, window=(x0, y0, 64, 4))
+    om = orc["sum"] / 64
+    assert np.allclose(mean[y0:y0 + 4, x0:x0 + 64].mean((0, 1)), om.mean((0, 1)), rtol=0.05)
+    # two of eight tile ranks reproduce their pixels bit-identically
+    for r in (0, 5):
+        _, ar, _ = _frame(core, W, H, pp, seed=1, tile_rank=r, tile_count=8)
+        mine = ar[..., 3] > 0
+        assert np.array_equal(ar[mine], a[mine]) and abs(mine.mean() - 1 / 8) < 0.01
