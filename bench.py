@@ -159,7 +159,9 @@ def run_b200(a):
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    stream = torch.cuda.current_stream()
+    # a non-default stream: torch events, NCCL and the library's kernels all order on it
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
     kern = {"auto": T.KERNEL_AUTO, "mega": T.KERNEL_MEGA, "wavefront": T.KERNEL_WAVEFRONT}[a.kernel]
     core = render.RenderCore(local, kernel=kern, stream=stream.cuda_stream)
     hw = host.HostWorld(a.world)

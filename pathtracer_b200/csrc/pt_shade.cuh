@@ -52,7 +52,7 @@ __device__ __forceinline__ float3 pt_schlick_metal(float F0, float c, float meta
 
 // PdfValue<TO_SPHERE_PDF>, main.cpp:324-340: 1/solid angle if the direction hits the light, else 0
 __device__ __forceinline__ float pt_pdf_to_sphere(float3 dir, float4 light, float3 from) {
-    float t = pt_sphere_t(from, dir, dot3(dir, dir), light);
+    float t = pt_sphere_t(from, dir, pt_dot_exact(dir), light);
     if (!(t > 0.f)) return 0.f;
     float3 rel = f3(from.x - light.x, from.y - light.y, from.z - light.z);
     float cmax = sqrtf(1.f - __fdividef(light.w * light.w, dot3(rel, rel)));

@@ -118,44 +118,59 @@ def test_render_same_streams_vs_oracle(core, worlds, w, lens, flags):
     assert (bgra >> 24 == 255).all()
 
 
+def _zstats(mu_gpu, se_gpu2, s, s2, n):
+    mu = s / n
+    var = np.maximum(s2 / n - mu ** 2, 0) * n / (n - 1)
+    se = np.sqrt(var / n + se_gpu2)
+    ok = se > 1e-9
+    z = (mu_gpu - mu)[ok] / se[ok]
+    npx = mu.shape[0] * mu.shape[1]
+    g_se = np.sqrt((var / n + se_gpu2).sum((0, 1))) / npx
+    g_z = (mu_gpu.mean((0, 1)) - mu.mean((0, 1))) / np.maximum(g_se, 1e-12)
+    return dict(frac3=float((np.abs(z) > 3).mean()), med=float(np.median(z)), g_z=g_z, ok=ok, mu=mu)
+
+
 @pytest.mark.parametrize("name,w,lens,flags", [
     ("hdr_w1.npz", 1, False, 7), ("hdr_w2.npz", 2, False, 7), ("hdr_w3.npz", 3, False, 7),
     ("hdr_w4.npz", 4, False, 7), ("hdr_w5.npz", 5, False, 7),
     ("hdr_w3_lens.npz", 3, True, 7), ("hdr_w1_nmr.npz", 1, False, 0)])
 def test_image_within_monte_carlo_error_of_reference(core, worlds, name, w, lens, flags):
     """Statistical parity against the REFERENCE's own render (fixture: per-pixel sum and sum of squares of
-    its mt19937 samples).  The GPU renders the same pixels with 16x the samples, so its own error is small;
-    z = (mu_gpu - mu_ref) / sqrt(se_ref^2 + se_gpu^2) must look like N(0,1): no bias, few outliers."""
+    its mt19937 samples, tools/make_golden.py).  The GPU renders the same pixels with 16x the samples from
+    8 seeds (so its own error is small and measured); z = (mu_gpu - mu_ref)/sqrt(se_ref^2 + se_gpu^2).
+
+    The estimator is heavy-tailed (sun radiance 15 x weights 2/px; 64..576 spp), so z is NOT N(0,1) even
+    for the reference against itself.  The test therefore calibrates against the null: the same statistic
+    with two fresh draws of the reference's estimator (the oracle, bit-exact with the reference, mt19937
+    seeds 99/100, same spp) in place of the fixture.  The fixture must be indistinguishable from them:
+      * fraction of pixel-channels beyond 3 sigma no larger than the null's (x1.6 + 1 %);
+      * median z within 0.2 of the null's; global image mean within 5 standard errors per channel."""
     g = golden(name)
     pp = int(g["pp"])
     n = pp * pp
     W, H = 48, 27
     sc = worlds(w).scene(W, H, lens=lens, tex_flags=flags)
     core.upload_scene(sc)
-    gpp = pp * 4
-    # per-pixel variance of the GPU estimate from 8 independent seeds
     means = []
     for seed in range(8):
-        core.render(W, H, gpp, seed=1000 + seed)
+        core.render(W, H, pp * 4, seed=1000 + seed)
         _, acc, _ = core.readback(False, True)
         means.append(acc[..., :3].astype(np.float64) / acc[..., 3:4])
     means = np.stack(means)
     mu_gpu = means.mean(0)
     se_gpu2 = means.var(0, ddof=1) / len(means)
-    mu_ref = g["sum"] / n
-    var_ref = np.maximum(g["sumsq"] / n - mu_ref ** 2, 0) * n / (n - 1)
-    se_ref2 = var_ref / n
-    se = np.sqrt(se_ref2 + se_gpu2)
-    ok = se > 1e-9
-    z = (mu_gpu - mu_ref)[ok] / se[ok]
-    # pixels the reference saw with zero variance (pure sky / constant): means must be equal
-    flat = ~ok
+    ref = _zstats(mu_gpu, se_gpu2, g["sum"], g["sumsq"], n)
+    nulls = []
+    for seed in (99, 100):
+        O.seed_mt(seed)
+        r = O.render(sc, W, H, pp, O.RNG_MT19937)
+        nulls.append(_zstats(mu_gpu, se_gpu2, r["sum"], r["sumsq"], n))
+    null_frac3 = max(x["frac3"] for x in nulls)
+    null_med = np.mean([x["med"] for x in nulls])
+    flat = ~ref["ok"]                     # pixels the reference saw with zero variance: means must be equal
     if flat.any():
-        assert np.allclose(mu_gpu[flat], mu_ref[flat], rtol=2e-3, atol=2e-3)
-    frac3 = (np.abs(z) > 3).mean()
-    # heavy-tailed pixels (sun radiance 15 x weights 2/px) make the reference's OWN se estimate noisy,
-    # so allow more 3-sigma outliers than a Gaussian's 0.27 %
-    assert frac3 < 0.03, f"{frac3:.4f} of pixel-channels beyond 3 sigma"
-    assert abs(np.median(z)) < 0.15, f"median z {np.median(z):.3f} (bias)"
-    # global energy: image means agree within 1 %
-    assert np.allclose(mu_gpu.mean((0, 1)), mu_ref.mean((0, 1)), rtol=1.5e-2)
+        assert np.allclose(mu_gpu[flat], ref["mu"][flat], rtol=2e-3, atol=2e-3)
+    assert ref["frac3"] <= 1.6 * null_frac3 + 0.01, (ref["frac3"], null_frac3)
+    assert abs(ref["med"] - null_med) < 0.2, (ref["med"], null_med)
+    assert (np.abs(ref["g_z"]) < 5).all(), ref["g_z"]
+    assert np.allclose(mu_gpu.mean((0, 1)), ref["mu"].mean((0, 1)), rtol=0.08)

@@ -210,7 +210,7 @@ def test_headline_config_properties(core, worlds):
     x0, y0 = 930, 500
     orc = O.render(sc, W, H, 8, O.RNG_PHILOX, 77, window=(x0, y0, 64, 4))
     om = orc["sum"] / 64
-    assert np.allclose(mean[y0:y0 + 4, x0:x0 + 64].mean((0, 1)), om.mean((0, 1)), rtol=0.05)
+    assert np.allclose(mean[y0:y0 + 4, x0:x0 + 64].mean((0, 1)), om.mean((0, 1)), rtol=0.05, atol=2e-3)
     # two of eight tile ranks reproduce their pixels bit-identically
     for r in (0, 5):
         _, ar, _ = _frame(core, W, H, pp, seed=1, tile_rank=r, tile_count=8)
