@@ -130,6 +130,12 @@ static float rnd(rng_t *r) {   /* RandomUnilateral, math.hpp:250-259 */
     return u32_to_unit_float(r->buf[w]);
 }
 
+/* PHILOX mode only: skip to the next 4-uniform block.  Every iteration of RayCast's sampling loop starts
+   on a fresh block, so the CUDA kernels need exactly one Philox evaluation per path vertex. */
+static void rng_align_block(rng_t *r) {
+    if (r->mode == PTO_RNG_PHILOX) r->count = (r->count + 3u) & ~3u;
+}
+
 void pto_seed_mt(uint32_t seed) { mt_seed(&g_mt, seed); g_mt_seeded = 1; }
 void pto_random_mt(uint32_t n, float *out) { rng_t r; rng_mt(&r); for (uint32_t i = 0; i < n; i++) out[i] = rnd(&r); }
 float pto_philox_uniform(uint64_t seed, uint32_t a, uint32_t b, uint32_t tag, uint32_t k) {
@@ -432,6 +438,7 @@ static v3 ray_cast(const pt_scene *s, rng_t *rng, v3 o, v3 d, int depth) {
         const int just_cosine = (s->flags & PT_SCENE_JUST_COSINE) != 0;
 
         for (;;) {                                       /* do { ... } while(true), main.cpp:660-792 */
+            rng_align_block(rng);
             int specular = rnd(rng) > 0.5f;
 
             if (specular && effectively_smooth(roughness)) {

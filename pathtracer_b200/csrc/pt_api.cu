@@ -33,6 +33,7 @@ struct pt_context {
     std::vector<void *> scene_allocs;          // freed on re-upload / destroy
     PtDeviceScene scene{};
     bool has_scene = false;
+    uint32_t features = PT_F_ALL;              // PT_F_* of the uploaded scene -> k_render variant
     // frame
     int width = 0, height = 0;
     float4 *accum = nullptr;
@@ -183,6 +184,31 @@ static int upload_bvh(pt_context *ctx, const ptbvh::Result &r, PtBvh *out) {
     return PT_OK;
 }
 
+// Features of the uploaded scene (pt_device.cuh PT_F_*) -> the smallest k_render instantiation covering them.
+static uint32_t scene_features(const PtDeviceScene &D, const pt_scene *s) {
+    uint32_t f = 0;
+    for (uint32_t m = 0; m < s->n_materials; m++) {
+        const pt_material &mm = s->materials[m];
+        if (mm.albedo_tex | mm.metalness_tex | mm.roughness_tex | mm.normal_tex) f |= PT_F_TEX;
+    }
+    if (D.n_quads) f |= PT_F_QUADS;
+    if (D.n_aabbs) f |= PT_F_AABBS;
+    if (D.sphere_bvh.n_nodes) f |= PT_F_SPH_BVH;
+    if (D.tri_bvh.n_nodes) f |= PT_F_TRI_BVH;
+    if (!(D.flags & PT_SCENE_JUST_COSINE)) f |= PT_F_LIGHT;
+    return f;
+}
+
+#define PT_RENDER_VARIANTS(X) \
+    X(PT_F_TEX | PT_F_LIGHT) X(PT_F_SPH_BVH | PT_F_LIGHT) X(PT_F_QUADS | PT_F_LIGHT) X(PT_F_SPH_BVH) X(PT_F_TRI_BVH | PT_F_LIGHT) X(PT_F_ALL)
+
+static void launch_render(uint32_t features, unsigned blocks, cudaStream_t st, const PtDeviceScene &S, const PtRenderArgs &A) {
+    // first variant (listed from specialised to general) whose mask covers the scene's features
+#define X(M) if ((features & ~(uint32_t)(M)) == 0) { k_render<(M)><<<blocks, PT_RENDER_THREADS, 0, st>>>(S, A); return; }
+    PT_RENDER_VARIANTS(X)
+#undef X
+}
+
 extern "C" int pt_upload_scene(pt_context *ctx, const pt_scene *s) {
     if (!ctx || !s) return PT_ERR_INVALID_ARG;
     if (s->struct_size != sizeof(pt_scene)) return fail(ctx, PT_ERR_INVALID_ARG, "pt_upload_scene: struct_size mismatch");
@@ -329,6 +355,7 @@ extern "C" int pt_upload_scene(pt_context *ctx, const pt_scene *s) {
     D.cam = s->camera;
     CK(cudaStreamSynchronize(ctx->stream));     // the host vectors above go out of scope
     ctx->scene = D;
+    ctx->features = scene_features(D, s);
     ctx->has_scene = true;
     return PT_OK;
 }
@@ -406,9 +433,10 @@ extern "C" int pt_render(pt_context *ctx, const pt_render_params *p) {
             A.log2_sample_lanes = lS;
             uint32_t warps_per_tile = 1024u >> (5u - lS);                  // pixels per tile / pixels per warp
             uint64_t warps = (uint64_t)A.n_my_tiles * warps_per_tile;
-            uint64_t blocks = (warps + 7) / 8;
+            const uint32_t wpb = PT_RENDER_THREADS / 32;
+            uint64_t blocks = (warps + wpb - 1) / wpb;
             if (blocks > 0x7fffffffull) return fail(ctx, PT_ERR_UNSUPPORTED, "pt_render: frame too large for one launch");
-            k_render<<<(unsigned)blocks, 256, 0, ctx->stream>>>(ctx->scene, A);
+            launch_render(ctx->features, (unsigned)blocks, ctx->stream, ctx->scene, A);
             ctx->last_launches = 1;
         }
         CK(cudaGetLastError());

@@ -136,18 +136,29 @@ __device__ __forceinline__ float u32_to_unit(uint32_t x) {
     return fminf(__uint2float_rn(x) * 2.3283064365386963e-10f, 0.99999994f);
 }
 
+// One Philox block (4 uniforms) per path vertex: the camera uses block 0 (words 0,1), and every iteration of
+// RayCast's sampling loop (main.cpp:660) starts on the next block -- coin, [coin, r1, r2] or [z1, z2].
 struct PtRng {
-    uint32_t k0, k1, a, b, tag, count;
-    uint4 buf;
+    uint32_t k0, k1, a, b, tag, blk;
     __device__ __forceinline__ void init(uint64_t seed, uint32_t a_, uint32_t b_, uint32_t tag_) {
         k0 = (uint32_t)seed; k1 = (uint32_t)(seed >> 32);
-        a = a_; b = b_; tag = tag_; count = 0;
+        a = a_; b = b_; tag = tag_; blk = 0;
     }
-    __device__ __forceinline__ float next() {
-        uint32_t w = count & 3u;
-        if (w == 0) buf = philox4x32_10(count >> 2, a, b, tag, k0, k1);
-        count++;
-        uint32_t v = (w == 0) ? buf.x : (w == 1) ? buf.y : (w == 2) ? buf.z : buf.w;
-        return u32_to_unit(v);
+    __device__ __forceinline__ uint4 next_block() {
+        uint4 r = philox4x32_10(blk, a, b, tag, k0, k1);
+        blk++;
+        return r;
     }
+};
+
+// ---- compile-time scene features: one k_render instantiation per combination that occurs ---------------
+// (smaller code -> fewer instruction-cache misses, fewer registers -> more resident warps)
+enum : uint32_t {
+    PT_F_TEX = 1u,        // some material references a texture
+    PT_F_QUADS = 2u,
+    PT_F_AABBS = 4u,
+    PT_F_SPH_BVH = 8u,
+    PT_F_TRI_BVH = 16u,
+    PT_F_LIGHT = 32u,     // importance-sample spheres[0] (everything but PT_SCENE_JUST_COSINE)
+    PT_F_ALL = 63u
 };

@@ -6,6 +6,13 @@
 #include "pt_shade.cuh"
 #include "pt_trace.cuh"
 
+#ifndef PT_RENDER_THREADS
+#define PT_RENDER_THREADS 256
+#endif
+#ifndef PT_RENDER_MIN_BLOCKS
+#define PT_RENDER_MIN_BLOCKS 1
+#endif
+
 struct PtRenderArgs {
     int width, height, pp;
     uint32_t s_begin, s_end;            // sample range of the pp*pp list
@@ -39,8 +46,9 @@ __device__ __forceinline__ void pt_camera_ray(const pt_camera &c, int W, int H, 
         const float stepX = inv_pp * c.half_pixel_w * 2.f, stepY = inv_pp * c.half_pixel_h * 2.f;
         float xs = (fx - c.half_pixel_w) + (float)i * inv_pp * c.half_pixel_w + stepX * 0.5f;
         float ys = (fy - c.half_pixel_h) + (float)j * inv_pp * c.half_pixel_h + stepY * 0.5f;
-        xs += (rng.next() - 0.5f) * stepX;
-        ys += (rng.next() - 0.5f) * stepY;
+        const uint4 u = rng.next_block();                     // block 0 of the path stream: the two jitters
+        xs += (u32_to_unit(u.x) - 0.5f) * stepX;
+        ys += (u32_to_unit(u.y) - 0.5f) * stepY;
         float3 P = fc + (xs * c.half_film_w) * ax + (ys * c.half_film_h) * ay;
         o = pos;
         d = normalize3(P - pos);
@@ -69,7 +77,8 @@ __device__ __forceinline__ void pt_camera_ray(const pt_camera &c, int W, int H, 
 // loop iteration each live lane advances its path by ONE segment (trace + shade); a lane whose path
 // ended starts its next sample in the same iteration (path regeneration), so lanes at different
 // depths share the instruction stream instead of idling behind the longest path.
-__global__ void __launch_bounds__(256)
+template <uint32_t F>
+__global__ void __launch_bounds__(PT_RENDER_THREADS, PT_RENDER_MIN_BLOCKS)
 k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRenderArgs A) {
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -109,16 +118,16 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
         }
         if (!__any_sync(0xffffffffu, alive)) break;
         if (alive) {
-            PtHit h = pt_closest_hit(S, o, d);
+            PtHit h = pt_closest_hit<F>(S, o, d);
             n_rays++;
             float3 n;
             uint32_t mat;
-            pt_hit_surface(S, h, o, d, n, mat);
+            pt_hit_surface<F>(S, h, o, d, n, mat);
             float3 e = pt_load_emit(S, mat);
             L = L + beta * e;                                               // radiance += emitColor, main.cpp:799
             bool emissive = (e.x != 0.f) || (e.y != 0.f) || (e.z != 0.f);
             bool done = (mat == 0) || emissive || (depth == PT_MAX_BOUNCE_COUNT - 1);
-            if (!done) done = !pt_shade_vertex(S, rng, mat, n, h.t, o, d, beta);
+            if (!done) done = !pt_shade_vertex<F>(S, rng, mat, n, h.t, o, d, beta);
             depth++;
             if (done) {
                 alive = false;
@@ -205,7 +214,7 @@ __global__ void k_resolve_colors(const float *__restrict__ rgb, uint32_t *__rest
 __device__ __forceinline__ void pt_store_hit(const PtDeviceScene &S, const PtHit &h, float3 o, float3 d, pt_hit *out) {
     float3 n;
     uint32_t mat;
-    pt_hit_surface(S, h, o, d, n, mat);
+    pt_hit_surface<PT_F_ALL>(S, h, o, d, n, mat);
     pt_hit r;
     r.t = h.t;
     r.kind = (h.id == PT_ID_MISS) ? PT_HIT_MISS : (int32_t)(h.id >> 28);
@@ -220,7 +229,7 @@ __global__ void k_trace_rays(const __grid_constant__ PtDeviceScene S, const floa
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     float3 ro = f3(o[3 * i], o[3 * i + 1], o[3 * i + 2]), rd = f3(d[3 * i], d[3 * i + 1], d[3 * i + 2]);
-    PtHit h = pt_closest_hit(S, ro, rd);
+    PtHit h = pt_closest_hit<PT_F_ALL>(S, ro, rd);
     pt_store_hit(S, h, ro, rd, out + i);
 }
 
@@ -241,7 +250,7 @@ __global__ void k_primary_hits(const __grid_constant__ PtDeviceScene S, int W, i
     float m = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)));
     float3 rd = f3(__fdiv_rn(dx, m), __fdiv_rn(dy, m), __fdiv_rn(dz, m));
     float3 ro = f3(c.pos);
-    PtHit h = pt_closest_hit(S, ro, rd);
+    PtHit h = pt_closest_hit<PT_F_ALL>(S, ro, rd);
     pt_store_hit(S, h, ro, rd, out + i);
 }
 
@@ -251,7 +260,7 @@ __global__ void k_trace_paths(const __grid_constant__ PtDeviceScene S, const flo
     if (i >= n) return;
     PtRng rng;
     rng.init(seed, i, 0u, 2u);
-    float3 L = pt_trace_path(S, rng, f3(o[3 * i], o[3 * i + 1], o[3 * i + 2]), f3(d[3 * i], d[3 * i + 1], d[3 * i + 2]));
+    float3 L = pt_trace_path<PT_F_ALL>(S, rng, f3(o[3 * i], o[3 * i + 1], o[3 * i + 2]), f3(d[3 * i], d[3 * i + 1], d[3 * i + 2]));
     rgb[3 * i] = L.x; rgb[3 * i + 1] = L.y; rgb[3 * i + 2] = L.z;
 }
 

@@ -85,6 +85,7 @@ __device__ __forceinline__ float3 pt_load_emit(const PtDeviceScene &S, uint32_t 
 
 // Shade the vertex at o + t*d with geometric normal n.  On return true the path continues along (o, d)
 // with beta multiplied by 2/px * brdfTerm (main.cpp:780-781); false = no bounce (main.cpp:648, 733, 748).
+template <uint32_t F>
 __device__ __forceinline__ bool pt_shade_vertex(const PtDeviceScene &S, PtRng &rng, uint32_t mat_index, float3 n, float t,
                                                 float3 &o, float3 &d, float3 &beta) {
     PtSurface m;
@@ -95,16 +96,17 @@ __device__ __forceinline__ bool pt_shade_vertex(const PtDeviceScene &S, PtRng &r
     float f = __fdividef(1.003f - m.ior, 1.003f + m.ior);
     const float F0 = f * f;                                                  // main.cpp:600
     const float3 P = f3(fmaf(t, d.x, o.x), fmaf(t, d.y, o.y), fmaf(t, d.z, o.z));
-    const float3 pure = d - (2.0f * cos_theta) * n;                          // mirror about the GEOMETRIC normal
     const float3 V = -d;
 
     float metalness = m.metalness, roughness = m.roughness;
     float3 N = n;
-    if (m.metalness_tex != 0 && (S.flags & PT_SCENE_METALNESS_MAPS)) metalness = pt_sample_texture(S.tex[m.metalness_tex - 1], P.x, P.y).x;
-    if (m.roughness_tex != 0 && (S.flags & PT_SCENE_ROUGHNESS_MAPS)) roughness = pt_sample_texture(S.tex[m.roughness_tex - 1], P.x, P.y).x;
-    if (m.normal_tex != 0 && (S.flags & PT_SCENE_NORMAL_MAPS)) {
-        float3 c = pt_sample_texture(S.tex[m.normal_tex - 1], P.x, P.y);
-        N = normalize3(f3(2.f * c.x - 1.f, 2.f * c.y - 1.f, 2.f * c.z - 1.f));   // world-space, main.cpp:637-643
+    if (F & PT_F_TEX) {
+        if (m.metalness_tex != 0 && (S.flags & PT_SCENE_METALNESS_MAPS)) metalness = pt_sample_texture(S.tex[m.metalness_tex - 1], P.x, P.y).x;
+        if (m.roughness_tex != 0 && (S.flags & PT_SCENE_ROUGHNESS_MAPS)) roughness = pt_sample_texture(S.tex[m.roughness_tex - 1], P.x, P.y).x;
+        if (m.normal_tex != 0 && (S.flags & PT_SCENE_NORMAL_MAPS)) {
+            float3 c = pt_sample_texture(S.tex[m.normal_tex - 1], P.x, P.y);
+            N = normalize3(f3(2.f * c.x - 1.f, 2.f * c.y - 1.f, 2.f * c.z - 1.f));   // world-space, main.cpp:637-643
+        }
     }
 
     const float NdotV = dot3(N, V);
@@ -112,43 +114,39 @@ __device__ __forceinline__ bool pt_shade_vertex(const PtDeviceScene &S, PtRng &r
 
     float3 tx, ty, tz;
     pt_onb(N, tx, ty, tz);
-    const bool just_cosine = (S.flags & PT_SCENE_JUST_COSINE) != 0;          // main.cpp:654-655
     const bool smooth = roughness < 0.01f;                                   // EffectivelySmooth, main.cpp:1783-1786
     const float4 light = S.light;
+    const bool use_light = (F & PT_F_LIGHT) && !(S.flags & PT_SCENE_JUST_COSINE);   // main.cpp:654-655
 
     float3 L, H = f3(0, 0, 0);
-    float px;
+    float px = 1.f;
     bool specular;
     int guard = 0;
     for (;;) {
         if (++guard > 64) return false;      // the reference would spin (origin inside the light); give up
-        specular = rng.next() > 0.5f;                                        // main.cpp:661
+        const uint4 u = rng.next_block();    // one Philox block per iteration: coin, then [coin, r1, r2] or [z1, z2]
+        specular = u32_to_unit(u.x) > 0.5f;                                  // main.cpp:661
         if (specular && smooth) {
-            L = pure;
-            px = 1.f;
+            L = d - (2.0f * cos_theta) * n;                                  // mirror about the GEOMETRIC normal, main.cpp:608
         } else if (!specular) {
-            bool sample_cosine = rng.next() > 0.5f;                          // main.cpp:678
+            bool sample_cosine = u32_to_unit(u.y) > 0.5f;                    // main.cpp:678
             float3 r;
-            if (sample_cosine || just_cosine) {
+            float sn, cs;
+            sincospif(2.f * u32_to_unit(u.z), &sn, &cs);
+            const float r2 = u32_to_unit(u.w);
+            if (!use_light || sample_cosine) {
                 // RandomCosineDirectionHemisphere, main.cpp:2258-2268
-                float r1 = rng.next(), r2 = rng.next();
-                float sn, cs;
-                sincospif(2.f * r1, &sn, &cs);
                 float sr = sqrtf(r2);
                 r = f3(cs * sr, sn * sr, sqrtf(1.f - r2));
             } else {
                 // RandomToSphere, main.cpp:2332-2353; the basis is re-aimed at the light and STAYS so
                 float3 dirl = f3(light.x - P.x, light.y - P.y, light.z - P.z);
-                float ds = dot3(dirl, dirl);
-                float term1 = 1.f - __fdividef(light.w * light.w, ds);
+                float term1 = 1.f - __fdividef(light.w * light.w, dot3(dirl, dirl));
                 if (term1 < 0.f) {
                     r = f3(0, 0, 0);
                 } else {
-                    float r1 = rng.next(), r2 = rng.next();
                     float z = 1.f + r2 * (sqrtf(term1) - 1.f);
                     float st = sqrtf(1.f - z * z);
-                    float sn, cs;
-                    sincospif(2.f * r1, &sn, &cs);
                     r = f3(cs * st, sn * st, z);
                 }
                 pt_onb(dirl, tx, ty, tz);
@@ -159,22 +157,21 @@ __device__ __forceinline__ bool pt_shade_vertex(const PtDeviceScene &S, PtRng &r
             H = normalize3(L + V);
             // cosine pdf of the LOCAL sample (for light samples: measured from the cone axis, main.cpp:709)
             float pc = fmaxf(0.f, r.z * rsqrtf(dot3(r, r)) * (1.0f / PT_PI));
-            if (!just_cosine) px = 0.5f * pc + 0.5f * pt_pdf_to_sphere(L, light, P);
+            if (use_light) px = 0.5f * pc + 0.5f * pt_pdf_to_sphere(L, light, P);
             else px = pc;
             if (px == 0.f) continue;                                         // main.cpp:722
         } else {
             // RandomHalfVectorGGX, main.cpp:2271-2285: cos(theta) = sqrt((1-z2)/(1+z2(a2-1)))
             float a2 = roughness * roughness * roughness * roughness;
-            float z1 = rng.next(), z2 = rng.next();
+            float z2 = u32_to_unit(u.z);
             float ct = sqrtf(__fdividef(1.f - z2, 1.f + z2 * (a2 - 1.f)));
             float st = sqrtf(fmaxf(0.f, 1.f - ct * ct));
             float sn, cs;
-            sincospif(2.f * z1, &sn, &cs);
+            sincospif(2.f * u32_to_unit(u.y), &sn, &cs);
             float3 r = f3(cs * st, sn * st, ct);
             H = normalize3(f3(r.x * tx.x + r.y * ty.x + r.z * N.x, r.x * tx.y + r.y * ty.y + r.z * N.y,
                               r.x * tx.z + r.y * ty.z + r.z * N.z));
             L = (2.f * dot3(V, H)) * H - V;
-            px = 1.f;
         }
         break;
     }
@@ -204,7 +201,7 @@ __device__ __forceinline__ bool pt_shade_vertex(const PtDeviceScene &S, PtRng &r
     } else {
         // N.L * kd * albedo / pi with kd = (1 - ks)(1 - metalness), main.cpp:751-759, 772, 1595-1608
         float3 albedo = m.albedo;
-        if (m.albedo_tex != 0) albedo = pt_sample_texture(S.tex[m.albedo_tex - 1], P.x, P.y);
+        if ((F & PT_F_TEX) && m.albedo_tex != 0) albedo = pt_sample_texture(S.tex[m.albedo_tex - 1], P.x, P.y);
         float q = (1.f - metalness) * NdotL * (1.0f / PT_PI);
         brdf = f3(q * (1.f - ks.x) * albedo.x, q * (1.f - ks.y) * albedo.y, q * (1.f - ks.z) * albedo.z);
     }
@@ -216,18 +213,19 @@ __device__ __forceinline__ bool pt_shade_vertex(const PtDeviceScene &S, PtRng &r
 }
 
 // RayCast as a loop: L = sum_k beta_k * emit_k over at most 4 vertices (main.cpp:564, 799)
+template <uint32_t F>
 __device__ __forceinline__ float3 pt_trace_path(const PtDeviceScene &S, PtRng &rng, float3 o, float3 d) {
     float3 beta = f3(1, 1, 1), L = f3(0, 0, 0);
     for (int depth = 0; depth < PT_MAX_BOUNCE_COUNT; depth++) {
-        PtHit h = pt_closest_hit(S, o, d);
+        PtHit h = pt_closest_hit<F>(S, o, d);
         float3 n;
         uint32_t mat;
-        pt_hit_surface(S, h, o, d, n, mat);
+        pt_hit_surface<F>(S, h, o, d, n, mat);
         float3 e = pt_load_emit(S, mat);
         L = L + beta * e;
         bool emissive = (e.x != 0.f) || (e.y != 0.f) || (e.z != 0.f);
         if (mat == 0 || emissive || depth == PT_MAX_BOUNCE_COUNT - 1) break;   // main.cpp:579-590
-        if (!pt_shade_vertex(S, rng, mat, n, h.t, o, d, beta)) break;
+        if (!pt_shade_vertex<F>(S, rng, mat, n, h.t, o, d, beta)) break;
     }
     return L;
 }

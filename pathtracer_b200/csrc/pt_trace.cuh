@@ -74,129 +74,168 @@ __device__ __forceinline__ void pt_accept(PtHit &h, float t, uint32_t id) {
 }
 
 enum { PT_LEAF_SPHERES = 0, PT_LEAF_TRIS = 1 };
+#define PT_STACK_SENTINEL ((int)0x80000000)
 
-// Stack-based BVH2 walk, nearer child first, culled by the best t so far.
-template <int LEAF>
-__device__ __forceinline__ void pt_bvh_walk(const PtDeviceScene &S, const PtBvh &bvh, float3 o, float3 d, float a, PtHit &h) {
+struct PtRayInv {          // per-ray constants of the slab test
+    float3 inv, ood;
+};
+__device__ __forceinline__ PtRayInv pt_ray_inv(float3 o, float3 d) {
     // reciprocal direction with zero components nudged so that no inf*0 appears in the slab test
     float3 dd = f3(fabsf(d.x) < 1e-20f ? copysignf(1e-20f, d.x) : d.x,
                    fabsf(d.y) < 1e-20f ? copysignf(1e-20f, d.y) : d.y,
                    fabsf(d.z) < 1e-20f ? copysignf(1e-20f, d.z) : d.z);
-    float3 inv = f3(__frcp_rn(dd.x), __frcp_rn(dd.y), __frcp_rn(dd.z));
-    float3 ood = f3(o.x * inv.x, o.y * inv.y, o.z * inv.z);
+    PtRayInv r;
+    r.inv = f3(__frcp_rn(dd.x), __frcp_rn(dd.y), __frcp_rn(dd.z));
+    r.ood = f3(o.x * r.inv.x, o.y * r.inv.y, o.z * r.inv.z);
+    return r;
+}
 
-    int stack[PT_STACK_DEPTH];
-    int sp = 0;
-    int node = 0;
+// slab test of the two child boxes of one node against [0, tmax]; returns near/far entry distances
+__device__ __forceinline__ void pt_node_slabs(const float4 b0, const float4 b1, const float4 b2, const PtRayInv &r, float tmax,
+                                              bool &hl, bool &hr, float &ln, float &rn) {
+    float lx0 = fmaf(b0.x, r.inv.x, -r.ood.x), lx1 = fmaf(b0.w, r.inv.x, -r.ood.x);
+    float ly0 = fmaf(b0.y, r.inv.y, -r.ood.y), ly1 = fmaf(b1.x, r.inv.y, -r.ood.y);
+    float lz0 = fmaf(b0.z, r.inv.z, -r.ood.z), lz1 = fmaf(b1.y, r.inv.z, -r.ood.z);
+    ln = fmaxf(fmaxf(fminf(lx0, lx1), fminf(ly0, ly1)), fmaxf(fminf(lz0, lz1), 0.f));
+    float lf = fminf(fminf(fmaxf(lx0, lx1), fmaxf(ly0, ly1)), fminf(fmaxf(lz0, lz1), tmax)) * 1.0000004f;
+    float rx0 = fmaf(b1.z, r.inv.x, -r.ood.x), rx1 = fmaf(b2.y, r.inv.x, -r.ood.x);
+    float ry0 = fmaf(b1.w, r.inv.y, -r.ood.y), ry1 = fmaf(b2.z, r.inv.y, -r.ood.y);
+    float rz0 = fmaf(b2.x, r.inv.z, -r.ood.z), rz1 = fmaf(b2.w, r.inv.z, -r.ood.z);
+    rn = fmaxf(fmaxf(fminf(rx0, rx1), fminf(ry0, ry1)), fmaxf(fminf(rz0, rz1), 0.f));
+    float rf = fminf(fminf(fmaxf(rx0, rx1), fmaxf(ry0, ry1)), fminf(fmaxf(rz0, rz1), tmax)) * 1.0000004f;
+    hl = ln <= lf;
+    hr = rn <= rf;
+}
+
+// does the ray enter either child box of the root within [0, tmax]?  (the "needs deep traversal" test)
+__device__ __forceinline__ bool pt_bvh_root_hit(const PtBvh &bvh, const PtRayInv &r, float tmax) {
     const float4 *nodes = reinterpret_cast<const float4 *>(bvh.nodes);
-    while (true) {
-        if (node >= 0) {
-            const float4 b0 = __ldg(nodes + 4 * node), b1 = __ldg(nodes + 4 * node + 1), b2 = __ldg(nodes + 4 * node + 2);
-            const int4 link = __ldg(reinterpret_cast<const int4 *>(nodes + 4 * node + 3));
-            // left child slabs
-            float lx0 = fmaf(b0.x, inv.x, -ood.x), lx1 = fmaf(b0.w, inv.x, -ood.x);
-            float ly0 = fmaf(b0.y, inv.y, -ood.y), ly1 = fmaf(b1.x, inv.y, -ood.y);
-            float lz0 = fmaf(b0.z, inv.z, -ood.z), lz1 = fmaf(b1.y, inv.z, -ood.z);
-            float ln = fmaxf(fmaxf(fminf(lx0, lx1), fminf(ly0, ly1)), fmaxf(fminf(lz0, lz1), 0.f));
-            float lf = fminf(fminf(fmaxf(lx0, lx1), fmaxf(ly0, ly1)), fminf(fmaxf(lz0, lz1), h.t)) * 1.0000004f;
-            // right child slabs
-            float rx0 = fmaf(b1.z, inv.x, -ood.x), rx1 = fmaf(b2.y, inv.x, -ood.x);
-            float ry0 = fmaf(b1.w, inv.y, -ood.y), ry1 = fmaf(b2.z, inv.y, -ood.y);
-            float rz0 = fmaf(b2.x, inv.z, -ood.z), rz1 = fmaf(b2.w, inv.z, -ood.z);
-            float rn = fmaxf(fmaxf(fminf(rx0, rx1), fminf(ry0, ry1)), fmaxf(fminf(rz0, rz1), 0.f));
-            float rf = fminf(fminf(fmaxf(rx0, rx1), fmaxf(ry0, ry1)), fminf(fmaxf(rz0, rz1), h.t)) * 1.0000004f;
-            bool hl = ln <= lf, hr = rn <= rf;
-            if (hl && hr) {
-                bool left_first = ln <= rn;
-                int nearc = left_first ? link.x : link.y;
-                int farc = left_first ? link.y : link.x;
-                stack[sp++] = farc;
-                node = nearc;
-                continue;
-            } else if (hl) { node = link.x; continue; }
-            else if (hr) { node = link.y; continue; }
+    bool hl, hr;
+    float ln, rn;
+    pt_node_slabs(__ldg(nodes), __ldg(nodes + 1), __ldg(nodes + 2), r, tmax, hl, hr, ln, rn);
+    return hl || hr;
+}
+
+template <int LEAF>
+__device__ __forceinline__ void pt_leaf_test(const PtDeviceScene &S, int node, float3 o, float3 d, float a, PtHit &h) {
+    uint32_t enc = (uint32_t)(~node);
+    uint32_t first = enc & 0xFFFFFFu, count = enc >> 24;
+    for (uint32_t i = 0; i < count; i++) {
+        uint32_t pos = first + i;
+        if (LEAF == PT_LEAF_TRIS) {
+            const float4 *rec = reinterpret_cast<const float4 *>(S.tris + pos);
+            float t = pt_planar_t<false>(o, d, __ldg(rec), __ldg(rec + 1), __ldg(rec + 2), PT_MIN_HIT);
+            if (t > 0.f && t <= h.t) pt_accept(h, t, PT_ID(PT_HIT_TRIANGLE, __ldg(S.tri_ids + pos)));
         } else {
-            uint32_t enc = (uint32_t)(~node);
-            uint32_t first = enc & 0xFFFFFFu, count = enc >> 24;
-            for (uint32_t i = 0; i < count; i++) {
-                uint32_t pos = first + i;
-                if (LEAF == PT_LEAF_TRIS) {
-                    const float4 *rec = reinterpret_cast<const float4 *>(S.tris + pos);
-                    float t = pt_planar_t<false>(o, d, __ldg(rec), __ldg(rec + 1), __ldg(rec + 2), PT_MIN_HIT);
-                    if (t > 0.f && t <= h.t) pt_accept(h, t, PT_ID(PT_HIT_TRIANGLE, __ldg(S.tri_ids + pos)));
-                } else {
-                    float t = pt_sphere_t(o, d, a, __ldg(S.bvh_spheres + pos));
-                    if (t > 0.f && t <= h.t) pt_accept(h, t, PT_ID(PT_HIT_SPHERE, __ldg(S.bvh_sphere_ids + pos)));
-                }
-            }
+            float t = pt_sphere_t(o, d, a, __ldg(S.bvh_spheres + pos));
+            if (t > 0.f && t <= h.t) pt_accept(h, t, PT_ID(PT_HIT_SPHERE, __ldg(S.bvh_sphere_ids + pos)));
         }
-        if (sp == 0) break;
-        node = stack[--sp];
     }
 }
 
-// closest hit over the whole scene; h.id == PT_ID_MISS and h.t == FLT_MAX on a miss (main.cpp:411-412)
-__device__ __forceinline__ PtHit pt_closest_hit(const PtDeviceScene &S, float3 o, float3 d) {
-    PtHit h;
-    h.t = 3.402823466e+38f;
-    h.id = PT_ID_MISS;
-    const float a = pt_dot_exact(d);
+// Stack-based BVH2 walk in "while-while" form: every lane first descends inner nodes until it holds a
+// leaf (nearer child first, culled by the best t so far), then the lanes test their leaves together.
+template <int LEAF>
+__device__ __forceinline__ void pt_bvh_walk(const PtDeviceScene &S, const PtBvh &bvh, float3 o, float3 d, float a, PtHit &h) {
+    const PtRayInv r = pt_ray_inv(o, d);
+    int stack[PT_STACK_DEPTH];
+    stack[0] = PT_STACK_SENTINEL;
+    int sp = 1;
+    int node = 0;
+    const float4 *nodes = reinterpret_cast<const float4 *>(bvh.nodes);
+    while (node != PT_STACK_SENTINEL) {
+        while (node >= 0) {
+            const float4 b0 = __ldg(nodes + 4 * node), b1 = __ldg(nodes + 4 * node + 1), b2 = __ldg(nodes + 4 * node + 2);
+            const int4 link = __ldg(reinterpret_cast<const int4 *>(nodes + 4 * node + 3));
+            bool hl, hr;
+            float ln, rn;
+            pt_node_slabs(b0, b1, b2, r, h.t, hl, hr, ln, rn);
+            if (hl && hr) {
+                bool left_first = ln <= rn;
+                stack[sp++] = left_first ? link.y : link.x;
+                node = left_first ? link.x : link.y;
+            } else if (hl) node = link.x;
+            else if (hr) node = link.y;
+            else node = stack[--sp];
+        }
+        if (node != PT_STACK_SENTINEL) {
+            pt_leaf_test<LEAF>(S, node, o, d, a, h);
+            node = stack[--sp];
+        }
+    }
+}
+
+// the analytic (linear-list) part of the closest hit: spheres, quads, planes, boxes
+template <uint32_t F>
+__device__ __forceinline__ void pt_hit_analytic(const PtDeviceScene &S, float3 o, float3 d, float a, PtHit &h) {
     for (uint32_t i = 0; i < S.n_lin_spheres; i++) {
         float t = pt_sphere_t(o, d, a, __ldg(S.lin_spheres + i));
         if (t > 0.f && t <= h.t) pt_accept(h, t, PT_ID(PT_HIT_SPHERE, __ldg(S.lin_sphere_ids + i)));
     }
-    for (uint32_t i = 0; i < S.n_quads; i++) {
-        const float4 *rec = reinterpret_cast<const float4 *>(S.quads + i);
-        float t = pt_planar_t<true>(o, d, __ldg(rec), __ldg(rec + 1), __ldg(rec + 2), PT_QUAD_MIN_HIT);
-        if (t > 0.f && t <= h.t) pt_accept(h, t, PT_ID(PT_HIT_QUAD, i));
+    if (F & PT_F_QUADS) {
+        for (uint32_t i = 0; i < S.n_quads; i++) {
+            const float4 *rec = reinterpret_cast<const float4 *>(S.quads + i);
+            float t = pt_planar_t<true>(o, d, __ldg(rec), __ldg(rec + 1), __ldg(rec + 2), PT_QUAD_MIN_HIT);
+            if (t > 0.f && t <= h.t) pt_accept(h, t, PT_ID(PT_HIT_QUAD, i));
+        }
     }
     for (uint32_t i = 0; i < S.n_planes; i++) {
         float t = pt_plane_t(o, d, __ldg(S.planes + i));
         if (t > PT_MIN_HIT && t <= h.t) pt_accept(h, t, PT_ID(PT_HIT_PLANE, i));
     }
-    if (S.sphere_bvh.n_prims) pt_bvh_walk<PT_LEAF_SPHERES>(S, S.sphere_bvh, o, d, a, h);
-    if (S.tri_bvh.n_prims) pt_bvh_walk<PT_LEAF_TRIS>(S, S.tri_bvh, o, d, a, h);
-    for (uint32_t i = 0; i < S.n_aabbs; i++) {
-        int face;
-        float t = pt_aabb_t(o, d, __ldg(S.aabbs + 2 * i), __ldg(S.aabbs + 2 * i + 1), &face);
-        if (t > PT_MIN_HIT && t <= h.t) pt_accept(h, t, PT_ID(PT_HIT_AABB, i));
+    if (F & PT_F_AABBS) {
+        for (uint32_t i = 0; i < S.n_aabbs; i++) {
+            int face;
+            float t = pt_aabb_t(o, d, __ldg(S.aabbs + 2 * i), __ldg(S.aabbs + 2 * i + 1), &face);
+            if (t > PT_MIN_HIT && t <= h.t) pt_accept(h, t, PT_ID(PT_HIT_AABB, i));
+        }
     }
+}
+
+// closest hit over the whole scene; h.id == PT_ID_MISS and h.t == FLT_MAX on a miss (main.cpp:411-412)
+template <uint32_t F>
+__device__ __forceinline__ PtHit pt_closest_hit(const PtDeviceScene &S, float3 o, float3 d) {
+    PtHit h;
+    h.t = 3.402823466e+38f;
+    h.id = PT_ID_MISS;
+    const float a = pt_dot_exact(d);
+    pt_hit_analytic<F>(S, o, d, a, h);
+    if ((F & PT_F_SPH_BVH) && S.sphere_bvh.n_prims) pt_bvh_walk<PT_LEAF_SPHERES>(S, S.sphere_bvh, o, d, a, h);
+    if ((F & PT_F_TRI_BVH) && S.tri_bvh.n_prims) pt_bvh_walk<PT_LEAF_TRIS>(S, S.tri_bvh, o, d, a, h);
     return h;
 }
 
 // geometric normal and material of a hit (ray_payload_t, include/ray.hpp:137-141)
+template <uint32_t F>
 __device__ __forceinline__ void pt_hit_surface(const PtDeviceScene &S, const PtHit &h, float3 o, float3 d,
                                                float3 &normal, uint32_t &mat) {
     uint32_t kind = h.id >> 28, idx = h.id & 0x0FFFFFFFu;
-    if (h.id == PT_ID_MISS) { normal = f3(0, 0, 0); mat = 0; return; }
-    switch (kind) {
-        case PT_HIT_SPHERE: {
-            float4 s = __ldg(S.all_spheres + idx);
-            // Normalize(t*dir + (origin - centre)), main.cpp:2374
-            normal = normalize3(f3(fmaf(h.t, d.x, o.x - s.x), fmaf(h.t, d.y, o.y - s.y), fmaf(h.t, d.z, o.z - s.z)));
-            mat = __ldg(S.sphere_mat + idx);
-        } break;
-        case PT_HIT_QUAD: {
-            float4 r0 = __ldg(reinterpret_cast<const float4 *>(S.quads + idx));
-            normal = f3(r0.x, r0.y, r0.z);
-            mat = __ldg(S.quad_mat + idx);
-        } break;
-        case PT_HIT_PLANE: {
-            float4 p = __ldg(S.planes + idx);
-            normal = f3(p.x, p.y, p.z);
-            mat = __ldg(S.plane_mat + idx);
-        } break;
-        case PT_HIT_TRIANGLE: {
-            float4 n = __ldg(S.tri_normals + idx);
-            normal = f3(n.x, n.y, n.z);
-            mat = __ldg(S.tri_mat + idx);
-        } break;
-        default: {
-            int face = 0;
-            pt_aabb_t(o, d, __ldg(S.aabbs + 2 * idx), __ldg(S.aabbs + 2 * idx + 1), &face);
-            const float nx[6] = {0.f, 0.f, -1.f, 1.f, 0.f, 0.f}, ny[6] = {0.f, 0.f, 0.f, 0.f, 1.f, -1.f}, nz[6] = {-1.f, 1.f, 0.f, 0.f, 0.f, 0.f};
-            normal = f3(nx[face], ny[face], nz[face]);     // face normal table, main.cpp:540-543
-            mat = __ldg(S.aabb_mat + idx);
-        } break;
+    normal = f3(0, 0, 0);
+    mat = 0;
+    if (h.id == PT_ID_MISS) return;
+    if (kind == PT_HIT_SPHERE) {
+        float4 s = __ldg(S.all_spheres + idx);
+        // Normalize(t*dir + (origin - centre)), main.cpp:2374
+        normal = normalize3(f3(fmaf(h.t, d.x, o.x - s.x), fmaf(h.t, d.y, o.y - s.y), fmaf(h.t, d.z, o.z - s.z)));
+        mat = __ldg(S.sphere_mat + idx);
+    } else if (kind == PT_HIT_PLANE) {
+        float4 p = __ldg(S.planes + idx);
+        normal = f3(p.x, p.y, p.z);
+        mat = __ldg(S.plane_mat + idx);
+    } else if ((F & PT_F_TRI_BVH) && kind == PT_HIT_TRIANGLE) {
+        float4 n = __ldg(S.tri_normals + idx);
+        normal = f3(n.x, n.y, n.z);
+        mat = __ldg(S.tri_mat + idx);
+    } else if ((F & PT_F_QUADS) && kind == PT_HIT_QUAD) {
+        float4 r0 = __ldg(reinterpret_cast<const float4 *>(S.quads + idx));
+        normal = f3(r0.x, r0.y, r0.z);
+        mat = __ldg(S.quad_mat + idx);
+    } else if ((F & PT_F_AABBS) && kind == PT_HIT_AABB) {
+        int face = 0;
+        pt_aabb_t(o, d, __ldg(S.aabbs + 2 * idx), __ldg(S.aabbs + 2 * idx + 1), &face);
+        // face normal table, main.cpp:540-543: -z +z -x +x +y -y
+        float sgn = (face == 0 || face == 2 || face == 5) ? -1.f : 1.f;
+        normal = f3((face == 2 || face == 3) ? sgn : 0.f, (face >= 4) ? sgn : 0.f, (face < 2) ? sgn : 0.f);
+        mat = __ldg(S.aabb_mat + idx);
     }
 }

@@ -12,7 +12,8 @@ import numpy as np
 from . import _ctypes_api as T
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libpt_b200.so")
+# PT_B200_LIB: another build of the same library (kernel experiments: tools/build_variants.sh)
+LIB_PATH = os.environ.get("PT_B200_LIB") or os.path.join(_HERE, "libpt_b200.so")
 
 _lib = None
 
