@@ -429,7 +429,8 @@ extern "C" int pt_render(pt_context *ctx, const pt_render_params *p) {
             // lanes of a warp that share a pixel: as many as the sample range allows (power of two <= 32)
             uint32_t lS = 0;
             while (lS < 5 && (2u << lS) <= n_samples) lS++;
-            if (ctx->sample_lanes_log2 >= 0) lS = std::min<uint32_t>(lS, (uint32_t)ctx->sample_lanes_log2);
+            // measured (profiles/r01b): 2..8 sample lanes x 16..4 adjacent pixels beat 32 lanes on one pixel
+            lS = std::min<uint32_t>(lS, ctx->sample_lanes_log2 >= 0 ? (uint32_t)ctx->sample_lanes_log2 : 3u);
             A.log2_sample_lanes = lS;
             uint32_t warps_per_tile = 1024u >> (5u - lS);                  // pixels per tile / pixels per warp
             uint64_t warps = (uint64_t)A.n_my_tiles * warps_per_tile;

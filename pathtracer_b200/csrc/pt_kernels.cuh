@@ -10,7 +10,7 @@
 #define PT_RENDER_THREADS 256
 #endif
 #ifndef PT_RENDER_MIN_BLOCKS
-#define PT_RENDER_MIN_BLOCKS 1
+#define PT_RENDER_MIN_BLOCKS 3
 #endif
 
 struct PtRenderArgs {
