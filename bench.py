@@ -137,6 +137,17 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": int(rows[0][1]), "reasons": reasons, "samples": len(rows)}
 
 
+def ncu_traffic(world):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one k_render launch from the committed `ncu --set full`
+    capture (profiles/k_render_traffic.json; the accumulator is read and written once per launch, so the figure
+    does not depend on spp); None where no capture exists for this world."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "k_render_traffic.json")))
+        return t.get(f"w{world}", {}).get("dram_bytes_per_launch")
+    except Exception:
+        return None
+
+
 def scene_bytes(sc):
     n = sc.n_materials * 68 + sc.n_spheres * 20 + sc.n_planes * 20 + sc.n_quads * 40 + sc.n_aabbs * 52 + sc.n_triangles * 40
     for i in range(4):
@@ -253,7 +264,7 @@ def run_b200(a):
             "frac": achieved_tf / fp32_peak if fp32_peak else None,
             "peak_source": "measured live: FMA-chain probe pt_measure_fp32_peak (nominal 148 SM x 128 x 2 x 1.965 GHz = 74.4)",
             "flops_per_sample": F_PER_SAMPLE[a.world], "kernel_ms": kernel_ms, "rays_per_sample": rays_per_sample,
-            "traffic": None,
+            "traffic": ncu_traffic(a.world),
             "hbm": {"bound": "hbm", "achieved": algo_bytes / (kernel_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                     "frac": algo_bytes / (kernel_ms * 1e-3) / 1e9 / hbm_peak,
                     "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s (B200_PROFILING.md)",

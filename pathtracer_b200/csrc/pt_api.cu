@@ -47,6 +47,7 @@ struct pt_context {
     uint32_t bvh_nodes = 0, bvh_prims = 0;
     PtWavefront wf;
     int sample_lanes_log2 = -1;                // -1 = auto
+    int shade_batch = 0;                       // PT_SHADE_BATCH: deferral threshold of k_render (0 = per-variant default)
 };
 
 #define CK(call)                                                                                     \
@@ -97,6 +98,12 @@ extern "C" int pt_create(const pt_config *cfg, pt_context **out) {
     if (cudaMalloc(&ctx->counters, 4 * sizeof(unsigned long long)) != cudaSuccess) { delete ctx; return fail(nullptr, PT_ERR_OOM, "cudaMalloc failed"); }
     cudaMemset(ctx->counters, 0, 4 * sizeof(unsigned long long));
     if (const char *s = getenv("PT_SAMPLE_LANES_LOG2")) ctx->sample_lanes_log2 = atoi(s);
+    if (const char *s = getenv("PT_SHADE_BATCH")) ctx->shade_batch = atoi(s);
+    if (const char *s = getenv("PT_WF_PIXELS_LOG2")) ctx->wf.pixels_log2 = atoi(s);
+    if (const char *s = getenv("PT_KERNEL")) {          // experiments: overrides pt_config.kernel
+        if (!strcmp(s, "mega")) ctx->kernel = PT_KERNEL_MEGA;
+        else if (!strcmp(s, "wavefront")) ctx->kernel = PT_KERNEL_WAVEFRONT;
+    }
     *out = ctx;
     return PT_OK;
 }
@@ -198,9 +205,6 @@ static uint32_t scene_features(const PtDeviceScene &D, const pt_scene *s) {
     if (!(D.flags & PT_SCENE_JUST_COSINE)) f |= PT_F_LIGHT;
     return f;
 }
-
-#define PT_RENDER_VARIANTS(X) \
-    X(PT_F_TEX | PT_F_LIGHT) X(PT_F_SPH_BVH | PT_F_LIGHT) X(PT_F_QUADS | PT_F_LIGHT) X(PT_F_SPH_BVH) X(PT_F_TRI_BVH | PT_F_LIGHT) X(PT_F_ALL)
 
 static void launch_render(uint32_t features, unsigned blocks, cudaStream_t st, const PtDeviceScene &S, const PtRenderArgs &A) {
     // first variant (listed from specialised to general) whose mask covers the scene's features
@@ -423,7 +427,7 @@ extern "C" int pt_render(pt_context *ctx, const pt_render_params *p) {
     if (n_samples > 0 && A.n_my_tiles > 0) {
         int kernel = ctx->kernel == PT_KERNEL_AUTO ? PT_KERNEL_MEGA : ctx->kernel;
         if (kernel == PT_KERNEL_WAVEFRONT) {
-            rc = ctx->wf.render(ctx->stream, ctx->scene, A, &ctx->last_launches, ctx->error);
+            rc = ctx->wf.render(ctx->stream, ctx->scene, A, ctx->features, &ctx->last_launches, ctx->error);
             if (rc) return rc;
         } else {
             // lanes of a warp that share a pixel: as many as the sample range allows (power of two <= 32)
@@ -432,6 +436,8 @@ extern "C" int pt_render(pt_context *ctx, const pt_render_params *p) {
             // measured (profiles/r01b): 2..8 sample lanes x 16..4 adjacent pixels beat 32 lanes on one pixel
             lS = std::min<uint32_t>(lS, ctx->sample_lanes_log2 >= 0 ? (uint32_t)ctx->sample_lanes_log2 : 3u);
             A.log2_sample_lanes = lS;
+            // parked lanes before the BRDF code runs (variants with PT_F_DEFER): measured best 32 with textures, else 20
+            A.shade_batch = ctx->shade_batch > 0 ? (uint32_t)ctx->shade_batch : ((ctx->features & PT_F_TEX) ? 32u : 20u);
             uint32_t warps_per_tile = 1024u >> (5u - lS);                  // pixels per tile / pixels per warp
             uint64_t warps = (uint64_t)A.n_my_tiles * warps_per_tile;
             const uint32_t wpb = PT_RENDER_THREADS / 32;

@@ -160,5 +160,6 @@ enum : uint32_t {
     PT_F_SPH_BVH = 8u,
     PT_F_TRI_BVH = 16u,
     PT_F_LIGHT = 32u,     // importance-sample spheres[0] (everything but PT_SCENE_JUST_COSINE)
-    PT_F_ALL = 63u
+    PT_F_ALL = 63u,
+    PT_F_DEFER = 64u      // kernel policy, not a scene feature: park lanes that need a BRDF sample (pt_kernels.cuh)
 };

@@ -7,11 +7,23 @@
 #include "pt_trace.cuh"
 
 #ifndef PT_RENDER_THREADS
-#define PT_RENDER_THREADS 256
+#define PT_RENDER_THREADS 128
 #endif
-#ifndef PT_RENDER_MIN_BLOCKS
-#define PT_RENDER_MIN_BLOCKS 3
+// CTAs per SM the register allocation aims at, per variant (measured, profiles/r01d_sweep_occupancy.log):
+// triangles 8 (64 regs, a few spills, +6 %), textures 6 (85 regs), everything else 7 (72 regs).
+// -DPT_RENDER_MIN_BLOCKS=n overrides it for all variants (tools/build_variants.sh).
+__host__ __device__ constexpr int pt_render_min_blocks(uint32_t F) {
+#ifdef PT_RENDER_MIN_BLOCKS
+    return PT_RENDER_MIN_BLOCKS;
+#else
+    return (F & PT_F_TEX) ? 6 : (F & PT_F_TRI_BVH) ? 8 : 7;
 #endif
+}
+
+// k_render / k_render_wf instantiations, from specialised to general: the first whose mask covers the scene runs
+#define PT_RENDER_VARIANTS(X) \
+    X(PT_F_TEX | PT_F_LIGHT | PT_F_DEFER) X(PT_F_SPH_BVH | PT_F_LIGHT) X(PT_F_QUADS | PT_F_LIGHT) X(PT_F_SPH_BVH) \
+    X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER) X(PT_F_ALL | PT_F_DEFER)
 
 struct PtRenderArgs {
     int width, height, pp;
@@ -19,6 +31,8 @@ struct PtRenderArgs {
     uint32_t tile_rank, tile_count;     // this launch renders tiles t with t % tile_count == tile_rank
     uint32_t tiles_x, tiles_y, n_my_tiles;
     uint32_t log2_sample_lanes;         // S = lanes of a warp that share one pixel; P = 32/S pixels per warp
+    uint32_t log2_pool_pixels;          // wavefront kernel: pixels per warp pool
+    uint32_t shade_batch;               // megakernel, PT_F_DEFER variants: parked lanes before the BRDF code runs
     uint64_t seed;
     float4 *accum;                      // width*height: sum r,g,b + number of samples
     unsigned long long *counters;       // [0] rays, [1] NaN retries, [2] samples
@@ -78,7 +92,7 @@ __device__ __forceinline__ void pt_camera_ray(const pt_camera &c, int W, int H, 
 // ended starts its next sample in the same iteration (path regeneration), so lanes at different
 // depths share the instruction stream instead of idling behind the longest path.
 template <uint32_t F>
-__global__ void __launch_bounds__(PT_RENDER_THREADS, PT_RENDER_MIN_BLOCKS)
+__global__ void __launch_bounds__(PT_RENDER_THREADS, pt_render_min_blocks(F))
 k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRenderArgs A) {
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -104,43 +118,83 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
     float3 acc = f3(0, 0, 0);
     float3 o = f3(0, 0, 0), d = f3(0, 0, 1), beta = f3(1, 1, 1), L = f3(0, 0, 0);
     int depth = 0;
-    bool alive = false;
+    PtHit h;
+    h.t = 3.402823466e+38f;
+    h.id = PT_ID_MISS;
     PtRng rng;
     rng.init(A.seed, 0, 0, 0);
 
+    // Lane states.  Where only ~30 % of the segments continue with a BRDF sample (w1, w5), shading right
+    // after the trace runs the longest straight-line code of the kernel at a third of the lanes.  With
+    // PT_F_DEFER a lane that needs a BRDF sample PARKS in NEED_SHADE while the others keep regenerating
+    // camera rays, until `shade_batch` lanes are parked (or nobody can regenerate); then the sampling code
+    // runs once for all of them.  Measured (profiles/r01d_sweep_defer.txt): w1 +18 %, w5 +8 %; it loses 3-5 %
+    // on w2/w3/w4, whose variants therefore shade at once.  The same deferral for the BVH walk lost everywhere.
+    // Scheduling never changes a sample's value: the Philox stream is keyed by (pixel, sample) and every
+    // lane adds its own samples in order.
+    enum { NO_RAY = 0, NEW_RAY = 1, NEED_SHADE = 2 };
+    uint32_t state = NO_RAY;
+
     while (true) {
-        if (!alive && s < A.s_end) {
+        if (state == NO_RAY && s < A.s_end) {
             pt_camera_ray(S.cam, A.width, A.height, A.pp, x, y, s, retry, A.seed, rng, o, d);
             beta = f3(1, 1, 1);
             L = f3(0, 0, 0);
             depth = 0;
-            alive = true;
+            state = NEW_RAY;
         }
-        if (!__any_sync(0xffffffffu, alive)) break;
-        if (alive) {
-            PtHit h = pt_closest_hit<F>(S, o, d);
+        const uint32_t n_live = __popc(__ballot_sync(0xffffffffu, state != NO_RAY));
+        if (n_live == 0) break;
+
+        // ---- closest hit, emission, termination rules of RayCast (main.cpp:579-590, 799) ----
+        bool done = false;
+        if (state == NEW_RAY) {
+            h = pt_closest_hit<F>(S, o, d);
             n_rays++;
             float3 n;
             uint32_t mat;
             pt_hit_surface<F>(S, h, o, d, n, mat);
-            float3 e = pt_load_emit(S, mat);
-            L = L + beta * e;                                               // radiance += emitColor, main.cpp:799
-            bool emissive = (e.x != 0.f) || (e.y != 0.f) || (e.z != 0.f);
-            bool done = (mat == 0) || emissive || (depth == PT_MAX_BOUNCE_COUNT - 1);
-            if (!done) done = !pt_shade_vertex<F>(S, rng, mat, n, h.t, o, d, beta);
-            depth++;
-            if (done) {
-                alive = false;
-                if (isnan3(L) && retry + 1 < PT_MAX_NAN_RETRIES) {
-                    retry++;                                                // redraw this sample, main.cpp:1068
-                    n_nan++;
-                } else {
-                    if (isnan3(L)) L = f3(0, 0, 0);
-                    acc = acc + L;
-                    n_acc++;
-                    s += Sn;
-                    retry = 0;
+            const float3 e = pt_load_emit(S, mat);
+            L = L + beta * e;
+            const bool emissive = (e.x != 0.f) || (e.y != 0.f) || (e.z != 0.f);
+            done = (mat == 0) || emissive || (depth == PT_MAX_BOUNCE_COUNT - 1);
+            if (!(F & PT_F_DEFER)) {
+                // shade at once, normal and material still in registers (best where most segments continue)
+                if (!done) done = !pt_shade_vertex<F>(S, rng, mat, n, h.t, o, d, beta);
+                depth++;
+            } else {
+                state = NEED_SHADE;
+            }
+        }
+
+        // ---- BRDF sample for the parked lanes (RayCast's sampling loop, main.cpp:657-781) ----
+        if (F & PT_F_DEFER) {
+            __syncwarp();
+            const uint32_t nS = __popc(__ballot_sync(0xffffffffu, state == NEED_SHADE && !done));
+            const uint32_t nD = __popc(__ballot_sync(0xffffffffu, done && s + Sn < A.s_end));   // lanes that will regenerate
+            if (nS >= A.shade_batch || nD == 0) {
+                if (state == NEED_SHADE && !done) {
+                    float3 n;
+                    uint32_t mat;
+                    pt_hit_surface<F>(S, h, o, d, n, mat);
+                    done = !pt_shade_vertex<F>(S, rng, mat, n, h.t, o, d, beta);
+                    depth++;
+                    state = NEW_RAY;
                 }
+            }
+            __syncwarp();
+        }
+        if (done) {
+            state = NO_RAY;
+            if (isnan3(L) && retry + 1 < PT_MAX_NAN_RETRIES) {
+                retry++;                                                    // redraw this sample, main.cpp:1068
+                n_nan++;
+            } else {
+                if (isnan3(L)) L = f3(0, 0, 0);
+                acc = acc + L;
+                n_acc++;
+                s += Sn;
+                retry = 0;
             }
         }
     }

@@ -108,6 +108,45 @@ def test_launch_shape_does_not_change_the_samples(worlds, lanes, monkeypatch):
     assert np.allclose(a[..., :3], b[..., :3], rtol=1e-5, atol=1e-5)
     rc.close(); rc2.close()
 
+@pytest.mark.parametrize("w,lens", [(1, False), (2, False), (3, False), (4, False), (5, False), (3, True), (5, True)])
+def test_wavefront_kernel_renders_the_same_samples(worlds, w, lens):
+    """PT_KERNEL_WAVEFRONT (paths pooled in shared memory, stage lists per warp) and the megakernel are two
+    schedules of the same samples: identical sample counts and ray counts, pixel sums equal up to float
+    summation order, LDR bytes equal except where a sum sits on a rounding boundary."""
+    W, H, pp = 150, 90, 6
+    sc = worlds(w).scene(W, H, lens=lens)
+    out = []
+    for kernel in (T.KERNEL_MEGA, T.KERNEL_WAVEFRONT):
+        rc = render.RenderCore(0, kernel=kernel)
+        rc.upload_scene(sc)
+        rc.render(W, H, pp, seed=3)
+        out.append(rc.readback(True, True))
+        rc.close()
+    (b0, a0, s0), (b1, a1, s1) = out
+    assert np.array_equal(a0[..., 3], a1[..., 3]) and s0.rays == s1.rays and s0.nan_retries == s1.nan_retries
+    assert np.allclose(a0[..., :3], a1[..., :3], rtol=2e-5, atol=1e-5)
+    assert (b0 == b1).mean() > 0.999
+
+
+@pytest.mark.parametrize("batch", [1, 8, 32])
+def test_shade_deferral_does_not_change_the_samples(worlds, batch, monkeypatch):
+    """Parking lanes until `shade_batch` of them need a BRDF sample is scheduling only: bit-identical sums."""
+    W, H, pp = 120, 80, 6
+    res = []
+    for b in (None, batch):
+        if b is None:
+            monkeypatch.delenv("PT_SHADE_BATCH", raising=False)
+        else:
+            monkeypatch.setenv("PT_SHADE_BATCH", str(b))
+        for w in (1, 5):
+            rc = render.RenderCore(0)
+            rc.upload_scene(worlds(w).scene(W, H))
+            rc.render(W, H, pp, seed=4)
+            res.append(rc.readback(False, True)[1])
+            rc.close()
+    monkeypatch.delenv("PT_SHADE_BATCH", raising=False)
+    assert np.array_equal(res[0], res[2]) and np.array_equal(res[1], res[3])
+
 
 @pytest.mark.parametrize("W,H,pp", [(1, 1, 3), (33, 31, 1), (31, 65, 2), (64, 64, 5)])
 def test_ragged_sizes_vs_oracle(core, worlds, W, H, pp):
