@@ -413,6 +413,7 @@ extern "C" int pt_render(pt_context *ctx, const pt_render_params *p) {
 
     PtRenderArgs A{};
     A.width = p->width; A.height = p->height; A.pp = p->pp;
+    A.pp_magic = p->pp > 1 ? (uint32_t)(0x100000000ull / (uint64_t)p->pp + 1ull) : 0xFFFFFFFFu;   // pp == 1: s == 0 only
     A.s_begin = p->sample_begin; A.s_end = s_end;
     A.tile_rank = p->tile_rank; A.tile_count = tile_count;
     A.tiles_x = (uint32_t)(p->width + PT_TILE - 1) / PT_TILE;

@@ -27,6 +27,7 @@ __host__ __device__ constexpr int pt_render_min_blocks(uint32_t F) {
 
 struct PtRenderArgs {
     int width, height, pp;
+    uint32_t pp_magic;                  // floor(2^32/pp)+1: s / pp == __umulhi(s, pp_magic) for s < pp*pp <= 10^6
     uint32_t s_begin, s_end;            // sample range of the pp*pp list
     uint32_t tile_rank, tile_count;     // this launch renders tiles t with t % tile_count == tile_rank
     uint32_t tiles_x, tiles_y, n_my_tiles;
@@ -46,7 +47,7 @@ __constant__ float2 c_poisson_disk[12] = {   // main.cpp:1097-1110
     {0.53742981f, -0.47373420f}, {-0.26496911f, -0.41893023f}};
 
 // Camera ray of sample s of pixel (x,y); leaves rng positioned after the camera's own draws.
-__device__ __forceinline__ void pt_camera_ray(const pt_camera &c, int W, int H, int pp, int x, int y, uint32_t s,
+__device__ __forceinline__ void pt_camera_ray(const pt_camera &c, int W, int H, int pp, uint32_t pp_magic, int x, int y, uint32_t s,
                                               uint32_t retry, uint64_t seed, PtRng &rng, float3 &o, float3 &d) {
     const float fy = -1.0f + 2.0f * (float)y / (float)H;      // row 0 = bottom; pixel -> its lower-left corner
     const float fx = -1.0f + 2.0f * (float)x / (float)W;
@@ -55,7 +56,7 @@ __device__ __forceinline__ void pt_camera_ray(const pt_camera &c, int W, int H, 
     rng.init(seed, pixel, s, retry << 8);
     if (c.use_pinhole) {
         // stratum (i,j): origins advance by hpw/pp, each stratum is 2*hpw/pp wide (main.cpp:1044-1057)
-        const uint32_t i = s / (uint32_t)pp, j = s - i * (uint32_t)pp;
+        const uint32_t i = __umulhi(s, pp_magic), j = s - i * (uint32_t)pp;
         const float inv_pp = 1.f / (float)pp;
         const float stepX = inv_pp * c.half_pixel_w * 2.f, stepY = inv_pp * c.half_pixel_h * 2.f;
         float xs = (fx - c.half_pixel_w) + (float)i * inv_pp * c.half_pixel_w + stepX * 0.5f;
@@ -69,7 +70,7 @@ __device__ __forceinline__ void pt_camera_ray(const pt_camera &c, int W, int H, 
     } else {
         // outer film sample ri jittered +-1 pixel, focal point on the focal plane, lens point from the
         // Poisson table at (ri*r2) % 12 (main.cpp:1114-1161)
-        const uint32_t ri = s / (uint32_t)pp, r2 = s - ri * (uint32_t)pp;
+        const uint32_t ri = __umulhi(s, pp_magic), r2 = s - ri * (uint32_t)pp;
         uint4 fj = philox4x32_10(0u, pixel, ri, 1u, (uint32_t)seed, (uint32_t)(seed >> 32));
         float offX = fx + (2.0f * u32_to_unit(fj.x) - 1.0f) * c.half_pixel_w;
         float offY = fy + (2.0f * u32_to_unit(fj.y) - 1.0f) * c.half_pixel_h;
@@ -137,7 +138,7 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
 
     while (true) {
         if (state == NO_RAY && s < A.s_end) {
-            pt_camera_ray(S.cam, A.width, A.height, A.pp, x, y, s, retry, A.seed, rng, o, d);
+            pt_camera_ray(S.cam, A.width, A.height, A.pp, A.pp_magic, x, y, s, retry, A.seed, rng, o, d);
             beta = f3(1, 1, 1);
             L = f3(0, 0, 0);
             depth = 0;

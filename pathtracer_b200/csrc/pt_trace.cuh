@@ -85,7 +85,8 @@ __device__ __forceinline__ PtRayInv pt_ray_inv(float3 o, float3 d) {
                    fabsf(d.y) < 1e-20f ? copysignf(1e-20f, d.y) : d.y,
                    fabsf(d.z) < 1e-20f ? copysignf(1e-20f, d.z) : d.z);
     PtRayInv r;
-    r.inv = f3(__frcp_rn(dd.x), __frcp_rn(dd.y), __frcp_rn(dd.z));
+    // MUFU.RCP (<= 1 ulp): the slab test below is conservative by 4e-7 relative and the boxes are padded
+    r.inv = f3(__fdividef(1.0f, dd.x), __fdividef(1.0f, dd.y), __fdividef(1.0f, dd.z));
     r.ood = f3(o.x * r.inv.x, o.y * r.inv.y, o.z * r.inv.z);
     return r;
 }

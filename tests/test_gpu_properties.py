@@ -147,6 +147,26 @@ def test_shade_deferral_does_not_change_the_samples(worlds, batch, monkeypatch):
     monkeypatch.delenv("PT_SHADE_BATCH", raising=False)
     assert np.array_equal(res[0], res[2]) and np.array_equal(res[1], res[3])
 
+@pytest.mark.parametrize("w,W,H", [(2, 320, 180), (4, 320, 180), (5, 480, 270)])
+def test_device_lbvh_gives_the_same_hits_and_image(worlds, w, W, H):
+    """PT_BVH_DEVICE_LBVH (Morton -> radix sort -> Karras -> refit on the GPU) is another tree over the same
+    primitives with the same accept rule: identical primary ids and t, and -- since every sample then follows
+    the same path -- a bit-identical accumulator."""
+    sc = worlds(w).scene(W, H)
+    out = []
+    for bvh in (T.BVH_HOST_SAH, T.BVH_DEVICE_LBVH):
+        rc = render.RenderCore(0, bvh=bvh)
+        rc.upload_scene(sc)
+        hits = rc.primary_hits(W, H)
+        rc.render(W, H, 4, seed=6)
+        out.append((hits, rc.readback(True, True)))
+        rc.close()
+    (h0, (b0, a0, s0)), (h1, (b1, a1, s1)) = out
+    assert np.array_equal(h0["kind"], h1["kind"]) and np.array_equal(h0["index"], h1["index"]) and np.array_equal(h0["t"], h1["t"])
+    assert s0.rays == s1.rays
+    assert np.array_equal(a0, a1) and np.array_equal(b0, b1)
+    assert s1.bvh_nodes > 0 and s1.bvh_prims == s0.bvh_prims
+
 
 @pytest.mark.parametrize("W,H,pp", [(1, 1, 3), (33, 31, 1), (31, 65, 2), (64, 64, 5)])
 def test_ragged_sizes_vs_oracle(core, worlds, W, H, pp):
