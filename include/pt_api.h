@@ -200,6 +200,16 @@ int pt_set_stream(pt_context *ctx, void *cuda_stream);
 int pt_pack_tiles(pt_context *ctx, void *dst_dev, uint32_t tile_rank, uint32_t tile_count, uint32_t *n_tiles_out);
 int pt_unpack_tiles(pt_context *ctx, const void *src_dev, uint32_t tile_rank, uint32_t tile_count);
 
+/* Single-process multi-GPU (one context per device, same frame size): exchange over NVLink peer copies,
+ * ordered by events on the two contexts' streams -- the counterpart of the gather / reduce that
+ * torch.distributed does for one process per GPU.  No reference counterpart (CPU threads share g_image,
+ * main.cpp:107).
+ *   pt_gather_tiles_from: resolve + pack src's tiles {t : t % tile_count == tile_rank}, copy them to dst's
+ *                         device and unpack them into dst's BGRA frame.
+ *   pt_add_accum_from:    dst.accum += src.accum (sample-range sharding); dst must be resolved again. */
+int pt_gather_tiles_from(pt_context *dst, pt_context *src, uint32_t tile_rank, uint32_t tile_count);
+int pt_add_accum_from(pt_context *dst, pt_context *src);
+
 /* debug / parity exports */
 /* closest hit of n caller-supplied rays (origins, dirs: n*3 floats, host pointers) */
 int pt_trace_rays(pt_context *ctx, uint32_t n, const float *origins, const float *dirs, pt_hit *hits_out);

@@ -43,6 +43,9 @@ typedef struct pt_host_options {
     char    out_path[512];    /* --out (reference: "test.bmp", main.cpp:984) */
     char    res_dir[512];     /* --res (reference: "res\\", main.cpp:1459) */
     int32_t system_cores;     /* what "System has %d core(s)." printed */
+    int32_t snapshots;        /* --snapshots N: write the .BMP after each of N sample chunks (the reference's live
+                                 viewer, main.cpp:252-274, without a window) */
+    int32_t hdr_dump;         /* --hdr: also write <out>.hdr.bin (W*H float4: sum r,g,b + sample count) for image_compare */
 } pt_host_options;
 
 /* Parses argv with the reference's per-character scan; prints the same warnings/messages to stdout.

@@ -85,7 +85,8 @@ class HostOptions(C.Structure):
                 ("normals", C.c_int32), ("metalness", C.c_int32), ("roughness", C.c_int32), ("help", C.c_int32),
                 ("width", C.c_int32), ("height", C.c_int32), ("gpus", C.c_int32), ("shard_samples", C.c_int32),
                 ("seed", C.c_uint64), ("scene_seed", C.c_uint32), ("lbvh", C.c_int32), ("kernel", C.c_int32),
-                ("out_path", C.c_char * 512), ("res_dir", C.c_char * 512), ("system_cores", C.c_int32)]
+                ("out_path", C.c_char * 512), ("res_dir", C.c_char * 512), ("system_cores", C.c_int32),
+                ("snapshots", C.c_int32), ("hdr_dump", C.c_int32)]
 
 
 HIT_DTYPE = np.dtype([("t", "<f4"), ("kind", "<i4"), ("index", "<i4"), ("mat", "<u4"), ("normal", "<f4", 3)])

@@ -48,6 +48,11 @@ struct pt_context {
     PtWavefront wf;
     int sample_lanes_log2 = -1;                // -1 = auto
     int shade_batch = 0;                       // PT_SHADE_BATCH: deferral threshold of k_render (0 = per-variant default)
+    // single-process multi-GPU (pt_gather_tiles_from / pt_add_accum_from)
+    void *pack_buf = nullptr, *stage_buf = nullptr;
+    size_t pack_bytes = 0, stage_bytes = 0;
+    cudaEvent_t ev_sent = nullptr, ev_stage_free = nullptr;
+    bool stage_in_use = false;
 };
 
 #define CK(call)                                                                                     \
@@ -129,6 +134,10 @@ extern "C" int pt_destroy(pt_context *ctx) {
     free_frame(ctx);
     ctx->wf.release();
     if (ctx->counters) cudaFree(ctx->counters);
+    if (ctx->pack_buf) cudaFree(ctx->pack_buf);
+    if (ctx->stage_buf) cudaFree(ctx->stage_buf);
+    if (ctx->ev_sent) cudaEventDestroy(ctx->ev_sent);
+    if (ctx->ev_stage_free) cudaEventDestroy(ctx->ev_stage_free);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
@@ -536,6 +545,91 @@ extern "C" int pt_unpack_tiles(pt_context *ctx, const void *src, uint32_t rank, 
     uint32_t tiles_x = (uint32_t)(ctx->width + PT_TILE - 1) / PT_TILE, tiles_y = (uint32_t)(ctx->height + PT_TILE - 1) / PT_TILE;
     uint32_t n = my_tile_count(tiles_x * tiles_y, rank, count);
     if (n) k_unpack_tiles<<<(n * 1024u + 255u) / 256u, 256, 0, ctx->stream>>>(ctx->bgra, (const uint32_t *)src, ctx->width, ctx->height, tiles_x, rank, count, n);
+    CK(cudaGetLastError());
+    return PT_OK;
+}
+
+// ---- single-process multi-GPU: one context per device, exchange by peer copies over NVLink -----------
+// (the `pathtracer --gpus N` executable; torch.distributed/NCCL does the same job for one process per GPU)
+__global__ void k_add_accum(float4 *__restrict__ dst, const float4 *__restrict__ src, int n) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        float4 a = dst[i], b = src[i];
+        dst[i] = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
+    }
+}
+
+static int ensure_buf(pt_context *ctx, void **buf, size_t *have, size_t want) {
+    if (*have >= want) return PT_OK;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (*buf) cudaFree(*buf);
+    *buf = nullptr; *have = 0;
+    CK(cudaMalloc(buf, want));
+    *have = want;
+    return PT_OK;
+}
+
+static int peer_prepare(pt_context *dst, pt_context *src, size_t bytes, const char *who) {
+    if (!dst || !src || dst == src) return PT_ERR_INVALID_ARG;
+    if (!dst->accum || !src->accum) return fail(dst, PT_ERR_NO_FRAME, std::string(who) + ": both contexts need a rendered frame");
+    if (dst->width != src->width || dst->height != src->height) return fail(dst, PT_ERR_INVALID_ARG, std::string(who) + ": frame sizes differ");
+    int rc = ensure_buf(dst, &dst->stage_buf, &dst->stage_bytes, bytes);
+    if (rc) return rc;
+    if (!dst->ev_stage_free) { cudaSetDevice(dst->device); cudaEventCreateWithFlags(&dst->ev_stage_free, cudaEventDisableTiming); }
+    if (!src->ev_sent) { cudaSetDevice(src->device); cudaEventCreateWithFlags(&src->ev_sent, cudaEventDisableTiming); }
+    if (dst->device != src->device) {           // direct NVLink path where the topology allows it; a staged copy otherwise
+        int can = 0;
+        cudaDeviceCanAccessPeer(&can, dst->device, src->device);
+        if (can) { cudaSetDevice(dst->device); cudaDeviceEnablePeerAccess(src->device, 0); cudaSetDevice(src->device); cudaDeviceEnablePeerAccess(dst->device, 0); }
+        cudaGetLastError();                     // "already enabled" is fine
+    }
+    return PT_OK;
+}
+
+extern "C" int pt_gather_tiles_from(pt_context *dst, pt_context *src, uint32_t rank, uint32_t count) {
+    if (!dst || !src || count == 0 || rank >= count) return PT_ERR_INVALID_ARG;
+    uint32_t tiles_x = (uint32_t)(src->width + PT_TILE - 1) / PT_TILE, tiles_y = (uint32_t)(src->height + PT_TILE - 1) / PT_TILE;
+    uint32_t n = my_tile_count(tiles_x * tiles_y, rank, count);
+    size_t bytes = (size_t)n * PT_TILE * PT_TILE * sizeof(uint32_t);
+    int rc = peer_prepare(dst, src, bytes ? bytes : 16, "pt_gather_tiles_from");
+    if (rc) return rc;
+    if (n == 0) return PT_OK;
+    if ((rc = ensure_buf(src, &src->pack_buf, &src->pack_bytes, bytes))) { dst->error = src->error; return rc; }
+    if (!src->resolved && (rc = pt_resolve(src))) { dst->error = src->error; return rc; }
+    if (!dst->resolved && (rc = pt_resolve(dst))) return rc;      // my own tiles first; the gathered ones overwrite theirs
+    pt_context *ctx = dst;
+    CK(cudaSetDevice(src->device));
+    k_pack_tiles<<<(n * 1024u + 255u) / 256u, 256, 0, src->stream>>>(src->bgra, (uint32_t *)src->pack_buf, src->width, src->height, tiles_x, rank, count, n);
+    if (dst->stage_in_use) CK(cudaStreamWaitEvent(src->stream, dst->ev_stage_free, 0));     // the previous unpack still reads the stage
+    CK(cudaMemcpyPeerAsync(dst->stage_buf, dst->device, src->pack_buf, src->device, bytes, src->stream));
+    CK(cudaEventRecord(src->ev_sent, src->stream));
+    CK(cudaSetDevice(dst->device));
+    CK(cudaStreamWaitEvent(dst->stream, src->ev_sent, 0));
+    k_unpack_tiles<<<(n * 1024u + 255u) / 256u, 256, 0, dst->stream>>>(dst->bgra, (const uint32_t *)dst->stage_buf, dst->width, dst->height, tiles_x, rank, count, n);
+    CK(cudaEventRecord(dst->ev_stage_free, dst->stream));
+    dst->stage_in_use = true;
+    CK(cudaGetLastError());
+    return PT_OK;
+}
+
+extern "C" int pt_add_accum_from(pt_context *dst, pt_context *src) {
+    if (!dst || !src) return PT_ERR_INVALID_ARG;
+    size_t n = (size_t)dst->width * dst->height;
+    int rc = peer_prepare(dst, src, n * sizeof(float4), "pt_add_accum_from");
+    if (rc) return rc;
+    pt_context *ctx = dst;
+    CK(cudaSetDevice(src->device));
+    if (dst->stage_in_use) CK(cudaStreamWaitEvent(src->stream, dst->ev_stage_free, 0));
+    CK(cudaMemcpyPeerAsync(dst->stage_buf, dst->device, src->accum, src->device, n * sizeof(float4), src->stream));
+    CK(cudaEventRecord(src->ev_sent, src->stream));
+    CK(cudaSetDevice(dst->device));
+    CK(cudaStreamWaitEvent(dst->stream, src->ev_sent, 0));
+    k_add_accum<<<(unsigned)((n + 255) / 256), 256, 0, dst->stream>>>(dst->accum, (const float4 *)dst->stage_buf, (int)n);
+    CK(cudaEventRecord(dst->ev_stage_free, dst->stream));
+    dst->stage_in_use = true;
+    dst->samples_accumulated += src->samples_accumulated;
+    dst->resolved = false;
     CK(cudaGetLastError());
     return PT_OK;
 }

@@ -73,6 +73,8 @@ extern "C" void pt_host_print_help(void) {
     std::printf("\t--res DIR                     - Directory holding mario.glb and the rusty-metal textures.\n");
     std::printf("\t--lbvh                        - Build the BVH on the device (LBVH) instead of host SAH.\n");
     std::printf("\t--kernel mega|wavefront       - Force a render kernel.\n");
+    std::printf("\t--snapshots N                 - Write the image after each of N sample chunks (progressive view).\n");
+    std::printf("\t--hdr                         - Also dump the float accumulator to <out>.hdr.bin (for image_compare).\n");
 }
 
 extern "C" int pt_host_parse_args(int argc, char **argv, pt_host_options *o) {
@@ -115,6 +117,8 @@ extern "C" int pt_host_parse_args(int argc, char **argv, pt_host_options *o) {
             else if (key == "out") std::snprintf(o->out_path, sizeof(o->out_path), "%s", need());
             else if (key == "res") std::snprintf(o->res_dir, sizeof(o->res_dir), "%s", need());
             else if (key == "lbvh") o->lbvh = 1;
+            else if (key == "snapshots") o->snapshots = std::max(1, std::atoi(need()));
+            else if (key == "hdr") o->hdr_dump = 1;
             else if (key == "kernel") { std::string s = need(); o->kernel = s == "mega" ? PT_KERNEL_MEGA : s == "wavefront" ? PT_KERNEL_WAVEFRONT : PT_KERNEL_AUTO; }
             else std::printf("Warning: invalid program arugment --%s\n", key.c_str());
             continue;

@@ -167,6 +167,38 @@ def test_device_lbvh_gives_the_same_hits_and_image(worlds, w, W, H):
     assert np.array_equal(a0, a1) and np.array_equal(b0, b1)
     assert s1.bvh_nodes > 0 and s1.bvh_prims == s0.bvh_prims
 
+@pytest.mark.parametrize("G", [2, 3])
+def test_single_process_peer_gather_and_reduce(worlds, G):
+    """pt_gather_tiles_from / pt_add_accum_from (what `pathtracer --gpus N` uses): G contexts render their shards,
+    context 0 pulls the rest by peer copies.  Tiles: bit-identical to the unsharded frame.  Samples: equal up to
+    float summation order.  (Contexts share device 0 here; the copies are the same calls across devices.)"""
+    W, H, pp = 200, 130, 4
+    sc = worlds(5).scene(W, H)
+    one = render.RenderCore(0)
+    one.upload_scene(sc)
+    one.render(W, H, pp, seed=12)
+    b_ref, a_ref, _ = one.readback(True, True)
+    cores = [render.RenderCore(0) for _ in range(G)]
+    for c in cores:
+        c.upload_scene(sc)
+    for r, c in enumerate(cores):
+        c.render(W, H, pp, seed=12, tile_rank=r, tile_count=G)
+    for r in range(1, G):
+        cores[0].gather_tiles_from(cores[r], r, G)
+    b, _, _ = cores[0].readback(True, False)
+    assert np.array_equal(b, b_ref)
+    spp = pp * pp
+    for r, c in enumerate(cores):
+        c.render(W, H, pp, seed=12, sample_begin=r * spp // G, sample_end=(r + 1) * spp // G)
+    for r in range(1, G):
+        cores[0].add_accum_from(cores[r])
+    b2, a2, st = cores[0].readback(True, True)
+    assert (a2[..., 3] == spp).all() and st.samples == W * H * spp
+    assert np.allclose(a2[..., :3], a_ref[..., :3], rtol=2e-5, atol=1e-5)
+    assert (b2 == b_ref).mean() > 0.999
+    for c in cores + [one]:
+        c.close()
+
 
 @pytest.mark.parametrize("W,H,pp", [(1, 1, 3), (33, 31, 1), (31, 65, 2), (64, 64, 5)])
 def test_ragged_sizes_vs_oracle(core, worlds, W, H, pp):
