@@ -223,6 +223,8 @@ int pt_resolve_colors(pt_context *ctx, uint32_t n, const float *rgb, uint32_t *b
 /* measurement helper for the roofline: achieved FP32 FMA throughput of this device (TFLOP/s, best of 5
    runs of an 8-way-ILP FMA chain on every SM), timed with CUDA events on the context's stream */
 int pt_measure_fp32_peak(pt_context *ctx, float *tflops_out);
+/* measurement helper: memset a 256 MiB scratch buffer (> the 126 MB L2) on the context's stream */
+int pt_flush_l2(pt_context *ctx);
 
 #ifdef __cplusplus
 }

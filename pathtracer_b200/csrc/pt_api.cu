@@ -53,6 +53,9 @@ struct pt_context {
     size_t pack_bytes = 0, stage_bytes = 0;
     cudaEvent_t ev_sent = nullptr, ev_stage_free = nullptr;
     bool stage_in_use = false;
+    void *flush_buf = nullptr;                 // pt_flush_l2
+    size_t flush_bytes = 0;
+    int flush_value = 0;
 };
 
 #define CK(call)                                                                                     \
@@ -135,6 +138,7 @@ extern "C" int pt_destroy(pt_context *ctx) {
     ctx->wf.release();
     if (ctx->counters) cudaFree(ctx->counters);
     if (ctx->pack_buf) cudaFree(ctx->pack_buf);
+    if (ctx->flush_buf) cudaFree(ctx->flush_buf);
     if (ctx->stage_buf) cudaFree(ctx->stage_buf);
     if (ctx->ev_sent) cudaEventDestroy(ctx->ev_sent);
     if (ctx->ev_stage_free) cudaEventDestroy(ctx->ev_stage_free);
@@ -631,6 +635,17 @@ extern "C" int pt_add_accum_from(pt_context *dst, pt_context *src) {
     dst->samples_accumulated += src->samples_accumulated;
     dst->resolved = false;
     CK(cudaGetLastError());
+    return PT_OK;
+}
+
+// Measurement helper: overwrite a scratch buffer larger than L2 (126 MB) so the next launch starts cold.
+extern "C" int pt_flush_l2(pt_context *ctx) {
+    if (!ctx) return PT_ERR_INVALID_ARG;
+    const size_t bytes = (size_t)256 << 20;
+    int rc = ensure_buf(ctx, &ctx->flush_buf, &ctx->flush_bytes, bytes);
+    if (rc) return rc;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaMemsetAsync(ctx->flush_buf, ++ctx->flush_value, bytes, ctx->stream));
     return PT_OK;
 }
 

@@ -44,6 +44,7 @@ def lib():
         L.pt_device_buffers.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
                                         C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
         L.pt_set_stream.argtypes = [C.c_void_p, C.c_void_p]
+        L.pt_flush_l2.argtypes = [C.c_void_p]
         L.pt_gather_tiles_from.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]
         L.pt_add_accum_from.argtypes = [C.c_void_p, C.c_void_p]
         L.pt_pack_tiles.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint32)]
@@ -60,7 +61,7 @@ def lib():
 EXPORTS = ["pt_api_version", "pt_create", "pt_destroy", "pt_last_error", "pt_upload_scene", "pt_set_camera",
            "pt_render", "pt_synchronize", "pt_resolve", "pt_readback", "pt_device_buffers", "pt_set_stream",
            "pt_pack_tiles", "pt_unpack_tiles", "pt_gather_tiles_from", "pt_add_accum_from", "pt_trace_rays", "pt_primary_hits", "pt_trace_paths",
-           "pt_resolve_colors", "pt_measure_fp32_peak"]
+           "pt_resolve_colors", "pt_measure_fp32_peak", "pt_flush_l2"]
 
 
 def _p(a):
@@ -147,6 +148,9 @@ class RenderCore:
 
     def unpack_tiles(self, src_ptr, tile_rank, tile_count):
         self._ck(lib().pt_unpack_tiles(self._h, src_ptr, tile_rank, tile_count))
+
+    def flush_l2(self):
+        self._ck(lib().pt_flush_l2(self._h))
 
     def gather_tiles_from(self, src, tile_rank, tile_count):
         """Single-process multi-GPU: pulls `src`'s tiles into this context's frame by a peer copy."""
