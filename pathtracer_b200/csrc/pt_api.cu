@@ -216,6 +216,7 @@ static uint32_t scene_features(const PtDeviceScene &D, const pt_scene *s) {
     if (D.sphere_bvh.n_nodes) f |= PT_F_SPH_BVH;
     if (D.tri_bvh.n_nodes) f |= PT_F_TRI_BVH;
     if (!(D.flags & PT_SCENE_JUST_COSINE)) f |= PT_F_LIGHT;
+    if (!D.cam.use_pinhole) f |= PT_F_LENS;
     return f;
 }
 
@@ -381,6 +382,7 @@ extern "C" int pt_set_camera(pt_context *ctx, const pt_camera *cam) {
     if (!ctx || !cam) return PT_ERR_INVALID_ARG;
     if (!ctx->has_scene) return fail(ctx, PT_ERR_NO_SCENE, "pt_set_camera: no scene uploaded");
     ctx->scene.cam = *cam;
+    ctx->features = (ctx->features & ~(uint32_t)PT_F_LENS) | (cam->use_pinhole ? 0u : (uint32_t)PT_F_LENS);
     return PT_OK;
 }
 

@@ -160,6 +160,7 @@ enum : uint32_t {
     PT_F_SPH_BVH = 8u,
     PT_F_TRI_BVH = 16u,
     PT_F_LIGHT = 32u,     // importance-sample spheres[0] (everything but PT_SCENE_JUST_COSINE)
-    PT_F_ALL = 63u,
-    PT_F_DEFER = 64u      // kernel policy, not a scene feature: park lanes that need a BRDF sample (pt_kernels.cuh)
+    PT_F_ALL = 63u | 128u,
+    PT_F_DEFER = 64u,     // kernel policy, not a scene feature: park lanes that need a BRDF sample (pt_kernels.cuh)
+    PT_F_LENS = 128u      // thin-lens camera (-d, always in world 4); pinhole-only variants drop that code
 };

@@ -22,8 +22,10 @@ __host__ __device__ constexpr int pt_render_min_blocks(uint32_t F) {
 
 // k_render / k_render_wf instantiations, from specialised to general: the first whose mask covers the scene runs
 #define PT_RENDER_VARIANTS(X) \
-    X(PT_F_TEX | PT_F_LIGHT | PT_F_DEFER) X(PT_F_SPH_BVH | PT_F_LIGHT) X(PT_F_QUADS | PT_F_LIGHT) X(PT_F_SPH_BVH) \
-    X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER) X(PT_F_ALL | PT_F_DEFER)
+    X(PT_F_TEX | PT_F_LIGHT | PT_F_DEFER) X(PT_F_SPH_BVH | PT_F_LIGHT) X(PT_F_QUADS | PT_F_LIGHT) X(PT_F_SPH_BVH | PT_F_LENS) \
+    X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER) /* the same families with -d */ X(PT_F_TEX | PT_F_LIGHT | PT_F_DEFER | PT_F_LENS) \
+    X(PT_F_SPH_BVH | PT_F_LIGHT | PT_F_LENS) X(PT_F_QUADS | PT_F_LIGHT | PT_F_LENS) X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_LENS) \
+    X(PT_F_ALL | PT_F_DEFER)
 
 struct PtRenderArgs {
     int width, height, pp;
@@ -47,6 +49,7 @@ __constant__ float2 c_poisson_disk[12] = {   // main.cpp:1097-1110
     {0.53742981f, -0.47373420f}, {-0.26496911f, -0.41893023f}};
 
 // Camera ray of sample s of pixel (x,y); leaves rng positioned after the camera's own draws.
+template <uint32_t F>
 __device__ __forceinline__ void pt_camera_ray(const pt_camera &c, int W, int H, int pp, uint32_t pp_magic, int x, int y, uint32_t s,
                                               uint32_t retry, uint64_t seed, PtRng &rng, float3 &o, float3 &d) {
     const float fy = -1.0f + 2.0f * (float)y / (float)H;      // row 0 = bottom; pixel -> its lower-left corner
@@ -54,7 +57,7 @@ __device__ __forceinline__ void pt_camera_ray(const pt_camera &c, int W, int H, 
     const uint32_t pixel = (uint32_t)y * (uint32_t)W + (uint32_t)x;
     const float3 ax = f3(c.axis_x), ay = f3(c.axis_y), fc = f3(c.frustum_center), pos = f3(c.pos);
     rng.init(seed, pixel, s, retry << 8);
-    if (c.use_pinhole) {
+    if (!(F & PT_F_LENS) || c.use_pinhole) {
         // stratum (i,j): origins advance by hpw/pp, each stratum is 2*hpw/pp wide (main.cpp:1044-1057)
         const uint32_t i = __umulhi(s, pp_magic), j = s - i * (uint32_t)pp;
         const float inv_pp = 1.f / (float)pp;
@@ -138,7 +141,7 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
 
     while (true) {
         if (state == NO_RAY && s < A.s_end) {
-            pt_camera_ray(S.cam, A.width, A.height, A.pp, A.pp_magic, x, y, s, retry, A.seed, rng, o, d);
+            pt_camera_ray<F>(S.cam, A.width, A.height, A.pp, A.pp_magic, x, y, s, retry, A.seed, rng, o, d);
             beta = f3(1, 1, 1);
             L = f3(0, 0, 0);
             depth = 0;

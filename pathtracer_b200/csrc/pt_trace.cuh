@@ -121,6 +121,7 @@ template <int LEAF>
 __device__ __forceinline__ void pt_leaf_test(const PtDeviceScene &S, int node, float3 o, float3 d, float a, PtHit &h) {
     uint32_t enc = (uint32_t)(~node);
     uint32_t first = enc & 0xFFFFFFu, count = enc >> 24;
+#pragma unroll 1
     for (uint32_t i = 0; i < count; i++) {
         uint32_t pos = first + i;
         if (LEAF == PT_LEAF_TRIS) {
@@ -169,22 +170,26 @@ __device__ __forceinline__ void pt_bvh_walk(const PtDeviceScene &S, const PtBvh 
 // the analytic (linear-list) part of the closest hit: spheres, quads, planes, boxes
 template <uint32_t F>
 __device__ __forceinline__ void pt_hit_analytic(const PtDeviceScene &S, float3 o, float3 d, float a, PtHit &h) {
+#pragma unroll 1
     for (uint32_t i = 0; i < S.n_lin_spheres; i++) {
         float t = pt_sphere_t(o, d, a, __ldg(S.lin_spheres + i));
         if (t > 0.f && t <= h.t) pt_accept(h, t, PT_ID(PT_HIT_SPHERE, __ldg(S.lin_sphere_ids + i)));
     }
     if (F & PT_F_QUADS) {
+#pragma unroll 1
         for (uint32_t i = 0; i < S.n_quads; i++) {
             const float4 *rec = reinterpret_cast<const float4 *>(S.quads + i);
             float t = pt_planar_t<true>(o, d, __ldg(rec), __ldg(rec + 1), __ldg(rec + 2), PT_QUAD_MIN_HIT);
             if (t > 0.f && t <= h.t) pt_accept(h, t, PT_ID(PT_HIT_QUAD, i));
         }
     }
+#pragma unroll 1
     for (uint32_t i = 0; i < S.n_planes; i++) {
         float t = pt_plane_t(o, d, __ldg(S.planes + i));
         if (t > PT_MIN_HIT && t <= h.t) pt_accept(h, t, PT_ID(PT_HIT_PLANE, i));
     }
     if (F & PT_F_AABBS) {
+#pragma unroll 1
         for (uint32_t i = 0; i < S.n_aabbs; i++) {
             int face;
             float t = pt_aabb_t(o, d, __ldg(S.aabbs + 2 * i), __ldg(S.aabbs + 2 * i + 1), &face);
