@@ -103,8 +103,8 @@ extern "C" int pt_create(const pt_config *cfg, pt_context **out) {
     }
     cudaEventCreate(&ctx->ev0);
     cudaEventCreate(&ctx->ev1);
-    if (cudaMalloc(&ctx->counters, 4 * sizeof(unsigned long long)) != cudaSuccess) { delete ctx; return fail(nullptr, PT_ERR_OOM, "cudaMalloc failed"); }
-    cudaMemset(ctx->counters, 0, 4 * sizeof(unsigned long long));
+    if (cudaMalloc(&ctx->counters, PT_N_COUNTERS * sizeof(unsigned long long)) != cudaSuccess) { delete ctx; return fail(nullptr, PT_ERR_OOM, "cudaMalloc failed"); }
+    cudaMemset(ctx->counters, 0, PT_N_COUNTERS * sizeof(unsigned long long));
     if (const char *s = getenv("PT_SAMPLE_LANES_LOG2")) ctx->sample_lanes_log2 = atoi(s);
     if (const char *s = getenv("PT_SHADE_BATCH")) ctx->shade_batch = atoi(s);
     if (const char *s = getenv("PT_WF_PIXELS_LOG2")) ctx->wf.pixels_log2 = atoi(s);
@@ -420,7 +420,7 @@ extern "C" int pt_render(pt_context *ctx, const pt_render_params *p) {
     if (rc) return rc;
     if (p->flags & PT_RENDER_CLEAR) {
         CK(cudaMemsetAsync(ctx->accum, 0, (size_t)p->width * p->height * sizeof(float4), ctx->stream));
-        CK(cudaMemsetAsync(ctx->counters, 0, 4 * sizeof(unsigned long long), ctx->stream));
+        CK(cudaMemsetAsync(ctx->counters, 0, PT_N_COUNTERS * sizeof(unsigned long long), ctx->stream));
         ctx->samples_accumulated = 0;
     }
     ctx->resolved = false;
@@ -508,6 +508,18 @@ extern "C" int pt_readback(pt_context *ctx, uint32_t *bgra, float *accum_rgba, p
     if (accum_rgba) CK(cudaMemcpyAsync(accum_rgba, ctx->accum, n * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
     unsigned long long c[4] = {0, 0, 0, 0};
     if (stats) CK(cudaMemcpyAsync(c, ctx->counters, sizeof(c), cudaMemcpyDeviceToHost, ctx->stream));
+#ifdef PT_STATS_HIST
+    if (stats) {      // experiment build: BVH-walk occupancy histogram (tools/README)
+        unsigned long long hc[PT_N_COUNTERS];
+        CK(cudaMemcpyAsync(hc, ctx->counters, sizeof(hc), cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        unsigned long long walks = 0, steps = 0;
+        for (int k = 1; k <= 32; k++) { walks += hc[4 + k]; steps += hc[4 + 33 + k]; }
+        fprintf(stderr, "[pt_stats] lanes-at-entry : share of walk launches : share of node steps (thread-level)\n");
+        for (int k = 1; k <= 32; k++)
+            fprintf(stderr, "[pt_stats] %2d : %6.2f%% : %6.2f%%\n", k, 100.0 * hc[4 + k] / (double)(walks ? walks : 1), 100.0 * hc[4 + 33 + k] / (double)(steps ? steps : 1));
+    }
+#endif
     CK(cudaStreamSynchronize(ctx->stream));
     if (stats) {
         memset(stats, 0, sizeof(*stats));

@@ -27,6 +27,8 @@ __host__ __device__ constexpr int pt_render_min_blocks(uint32_t F) {
     X(PT_F_SPH_BVH | PT_F_LIGHT | PT_F_LENS) X(PT_F_QUADS | PT_F_LIGHT | PT_F_LENS) X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_LENS) \
     X(PT_F_ALL | PT_F_DEFER)
 
+#define PT_N_COUNTERS 72            // [0] rays [1] NaN retries [2] samples [3] -, then the PT_STATS_HIST experiment's histograms
+
 struct PtRenderArgs {
     int width, height, pp;
     uint32_t pp_magic;                  // floor(2^32/pp)+1: s / pp == __umulhi(s, pp_magic) for s < pp*pp <= 10^6
@@ -153,6 +155,9 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
         // ---- closest hit, emission, termination rules of RayCast (main.cpp:579-590, 799) ----
         bool done = false;
         if (state == NEW_RAY) {
+#ifdef PT_STATS_HIST
+            g_pt_hist = A.counters;
+#endif
             h = pt_closest_hit<F>(S, o, d);
             n_rays++;
             float3 n;

@@ -137,15 +137,75 @@ __device__ __forceinline__ void pt_leaf_test(const PtDeviceScene &S, int node, f
 
 // Stack-based BVH2 walk in "while-while" form: every lane first descends inner nodes until it holds a
 // leaf (nearer child first, culled by the best t so far), then the lanes test their leaves together.
+#ifdef PT_STATS_HIST
+__device__ unsigned long long *g_pt_hist;     // experiment build only
+#endif
 template <int LEAF>
 __device__ __forceinline__ void pt_bvh_walk(const PtDeviceScene &S, const PtBvh &bvh, float3 o, float3 d, float a, PtHit &h) {
     const PtRayInv r = pt_ray_inv(o, d);
+#ifdef PT_STATS_HIST
+    const bool enters = pt_bvh_root_hit(bvh, r, h.t);
+    const uint32_t n_enter = __popc(__ballot_sync(__activemask(), enters));
+    uint32_t my_steps = 0;
+#endif
     int stack[PT_STACK_DEPTH];
     stack[0] = PT_STACK_SENTINEL;
     int sp = 1;
     int node = 0;
     const float4 *nodes = reinterpret_cast<const float4 *>(bvh.nodes);
     while (node != PT_STACK_SENTINEL) {
+        while (node >= 0) {
+#ifdef PT_STATS_HIST
+            my_steps++;
+#endif
+            const float4 b0 = __ldg(nodes + 4 * node), b1 = __ldg(nodes + 4 * node + 1), b2 = __ldg(nodes + 4 * node + 2);
+            const int4 link = __ldg(reinterpret_cast<const int4 *>(nodes + 4 * node + 3));
+            bool hl, hr;
+            float ln, rn;
+            pt_node_slabs(b0, b1, b2, r, h.t, hl, hr, ln, rn);
+            if (hl && hr) {
+                bool left_first = ln <= rn;
+                stack[sp++] = left_first ? link.y : link.x;
+                node = left_first ? link.x : link.y;
+            } else if (hl) node = link.x;
+            else if (hr) node = link.y;
+            else node = stack[--sp];
+        }
+        if (node != PT_STACK_SENTINEL) {
+            pt_leaf_test<LEAF>(S, node, o, d, a, h);
+            node = stack[--sp];
+        }
+    }
+#ifdef PT_STATS_HIST
+    if (enters && g_pt_hist) {
+        atomicAdd(g_pt_hist + 4 + n_enter, 1ull);
+        atomicAdd(g_pt_hist + 4 + 33 + n_enter, (unsigned long long)my_steps);
+    }
+#endif
+}
+
+// The same walk as a resumable object: advance() descends to the next leaf, tests it and pops.  A lane can
+// therefore finish one ray and begin() another while its neighbours are still walking (the wavefront
+// kernel's BVH stage refills idle lanes from its ray list this way).
+template <int LEAF>
+struct PtWalker {
+    PtRayInv r;
+    float3 o, d;
+    float a;
+    PtHit h;
+    int node, sp;
+    int stack[PT_STACK_DEPTH];
+    __device__ __forceinline__ void begin(float3 o_, float3 d_, const PtHit &h0) {
+        o = o_; d = d_; h = h0;
+        a = pt_dot_exact(d_);
+        r = pt_ray_inv(o_, d_);
+        stack[0] = PT_STACK_SENTINEL;
+        sp = 1;
+        node = 0;
+    }
+    __device__ __forceinline__ bool done() const { return node == PT_STACK_SENTINEL; }
+    __device__ __forceinline__ void advance(const PtDeviceScene &S, const PtBvh &bvh) {
+        const float4 *nodes = reinterpret_cast<const float4 *>(bvh.nodes);
         while (node >= 0) {
             const float4 b0 = __ldg(nodes + 4 * node), b1 = __ldg(nodes + 4 * node + 1), b2 = __ldg(nodes + 4 * node + 2);
             const int4 link = __ldg(reinterpret_cast<const int4 *>(nodes + 4 * node + 3));
@@ -165,7 +225,7 @@ __device__ __forceinline__ void pt_bvh_walk(const PtDeviceScene &S, const PtBvh 
             node = stack[--sp];
         }
     }
-}
+};
 
 // the analytic (linear-list) part of the closest hit: spheres, quads, planes, boxes
 template <uint32_t F>

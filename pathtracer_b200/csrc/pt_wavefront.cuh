@@ -7,7 +7,10 @@
 //
 //     END   : the path ended (or the slot is fresh) -> accumulate, start the next sample (camera ray)
 //     SHADE : a surface was hit and the path continues -> BRDF sample, next ray
-//     BVH   : the new ray enters the root of a BVH    -> walk it
+//     BVH   : the new ray enters the root of a BVH    -> walk it; a lane whose ray is finished takes the
+//             next ray of the list at once (persistent refill), so the walk runs with full lanes until
+//             the list is empty instead of idling behind the longest ray
+//     HIT   : a walked ray has its final hit          -> emission, termination rules -> END or SHADE
 //
 // Every iteration the warp runs the stage with the MOST pending paths, up to 32 of them, one per lane.
 // END and SHADE finish with the cheap analytic part of the closest hit and the BVH-root test of their
@@ -28,15 +31,18 @@
 #ifndef PT_WF_MIN_BLOCKS
 #define PT_WF_MIN_BLOCKS 6
 #endif
+#ifndef PT_WF_REFILL
+#define PT_WF_REFILL 0           // 1: persistent BVH stage (idle lanes take the next ray of the list).  Correct (bit-identical
+#endif                           //    images) but measured slower with 64-path pools: 11.7 vs 13.0 Gsamples/s on w5 (profiles/r01e)
 
 enum { WF_OX, WF_OY, WF_OZ, WF_DX, WF_DY, WF_DZ, WF_BX, WF_BY, WF_BZ, WF_LX, WF_LY, WF_LZ,
        WF_AX, WF_AY, WF_AZ, WF_T, WF_ID, WF_S, WF_MISC, WF_FIELDS };
-enum { WF_BVH = 0, WF_END = 1, WF_SHADE = 2, WF_NONE = 3 };
+enum { WF_BVH = 0, WF_END = 1, WF_SHADE = 2, WF_HIT = 3, WF_NONE = 4 };
 #define WF_FRESH (1u << 24)      // misc: depth | retry << 8 | philox block << 16 | WF_FRESH
 
 struct PtWfWarp {                                  // shared memory of one warp: SoA, field-major
     float f[WF_FIELDS][PT_WF_POOL];                // path p of field k at bank (p % 32): <= POOL/32-way conflicts
-    uint8_t list[3][PT_WF_POOL];
+    uint8_t list[4][PT_WF_POOL];
 };
 
 __device__ __forceinline__ float3 wf_ld3(const PtWfWarp &W, int k, uint32_t p) { return f3(W.f[k][p], W.f[k + 1][p], W.f[k + 2][p]); }
@@ -66,7 +72,8 @@ k_render_wf(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtR
 #define WF_PIXEL_X(p) ((int)(x0 + (((p) & ((1u << lP) - 1u)) & ((1u << pw_log2) - 1u))))
 #define WF_PIXEL_Y(p) ((int)(y0 + (((p) & ((1u << lP) - 1u)) >> pw_log2)))
 
-    uint32_t nB = 0, nE = 0, nS = 0;          // list lengths (warp-uniform)
+    uint32_t nB = 0, nE = 0, nS = 0, nH = 0;  // list lengths (warp-uniform)
+    constexpr bool kOneBvh = PT_WF_REFILL && (((F & PT_F_SPH_BVH) != 0) != ((F & PT_F_TRI_BVH) != 0));   // refill needs one tree type
     uint32_t n_rays = 0, n_nan = 0;           // per-lane statistics
 
     // every slot starts "fresh" on the END list: END skips the accumulate and shoots the first camera ray
@@ -85,14 +92,15 @@ k_render_wf(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtR
         __syncwarp();
         // the fullest list runs next
         uint32_t st, cnt;
-        if (nB >= nE && nB >= nS) { st = WF_BVH; cnt = nB; }
+        if (nB >= nE && nB >= nS && nB >= nH) { st = WF_BVH; cnt = nB; }
+        else if (nH >= nE && nH >= nS) { st = WF_HIT; cnt = nH; }
         else if (nS >= nE) { st = WF_SHADE; cnt = nS; }
         else { st = WF_END; cnt = nE; }
         if (cnt == 0) break;
         const uint32_t take = cnt < 32u ? cnt : 32u;
-        const bool have = lane < take;
-        const uint32_t p = have ? (uint32_t)W.list[st][cnt - 1u - lane] : 0u;
-        if (st == WF_BVH) nB -= take; else if (st == WF_SHADE) nS -= take; else nE -= take;
+        bool have = lane < take;
+        uint32_t p = have ? (uint32_t)W.list[st][cnt - 1u - lane] : 0u;
+        if (st == WF_BVH) nB -= take; else if (st == WF_SHADE) nS -= take; else if (st == WF_HIT) nH -= take; else nE -= take;
 
         uint32_t dest = WF_NONE, misc = 0;
         bool has_ray = false, has_hit = false;
@@ -152,6 +160,58 @@ k_render_wf(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtR
                     dest = WF_END;                                           // no bounce: radiance so far stands
                 }
             }
+        } else if (st == WF_HIT) {
+            if (have) {
+                misc = __float_as_uint(W.f[WF_MISC][p]);
+                o = wf_ld3(W, WF_OX, p);
+                d = wf_ld3(W, WF_DX, p);
+                h.t = W.f[WF_T][p];
+                h.id = __float_as_uint(W.f[WF_ID][p]);
+                has_hit = true;
+            }
+        } else if (kOneBvh) {
+            // persistent walk: finished lanes hand their hit to the HIT list and take the next ray at once
+            constexpr int LEAF = (F & PT_F_TRI_BVH) ? PT_LEAF_TRIS : PT_LEAF_SPHERES;
+            const PtBvh &bvh = (F & PT_F_TRI_BVH) ? S.tri_bvh : S.sphere_bvh;
+            PtWalker<LEAF> wk;
+            bool walking = have;
+            if (walking) {
+                h.t = W.f[WF_T][p];
+                h.id = __float_as_uint(W.f[WF_ID][p]);
+                wk.begin(wf_ld3(W, WF_OX, p), wf_ld3(W, WF_DX, p), h);
+            } else {
+                wk.node = PT_STACK_SENTINEL;
+                wk.sp = 1;
+            }
+            while (true) {
+                const uint32_t idle = __ballot_sync(0xffffffffu, !walking);
+                if (idle != 0u && nB != 0u) {
+                    const uint32_t rank = __popc(idle & lt_mask);
+                    if (!walking && rank < nB) {
+                        p = (uint32_t)W.list[WF_BVH][nB - 1u - rank];
+                        h.t = W.f[WF_T][p];
+                        h.id = __float_as_uint(W.f[WF_ID][p]);
+                        wk.begin(wf_ld3(W, WF_OX, p), wf_ld3(W, WF_DX, p), h);
+                        walking = true;
+                    }
+                    const uint32_t n_idle = __popc(idle);
+                    nB -= n_idle < nB ? n_idle : nB;
+                }
+                if (!__any_sync(0xffffffffu, walking)) break;
+                if (walking) wk.advance(S, bvh);
+                const bool fin = walking && wk.done();
+                const uint32_t mF = __ballot_sync(0xffffffffu, fin);
+                if (mF != 0u) {
+                    if (fin) {
+                        W.f[WF_T][p] = wk.h.t;
+                        W.f[WF_ID][p] = __uint_as_float(wk.h.id);
+                        W.list[WF_HIT][nH + __popc(mF & lt_mask)] = (uint8_t)p;
+                        walking = false;
+                    }
+                    nH += __popc(mF);
+                }
+            }
+            have = false;                    // nothing left for the common tail
         } else {
             if (have) {
                 misc = __float_as_uint(W.f[WF_MISC][p]);
