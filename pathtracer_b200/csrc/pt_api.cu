@@ -449,8 +449,13 @@ extern "C" int pt_render(pt_context *ctx, const pt_render_params *p) {
             // lanes of a warp that share a pixel: as many as the sample range allows (power of two <= 32)
             uint32_t lS = 0;
             while (lS < 5 && (2u << lS) <= n_samples) lS++;
-            // measured (profiles/r01b): 2..8 sample lanes x 16..4 adjacent pixels beat 32 lanes on one pixel
-            lS = std::min<uint32_t>(lS, ctx->sample_lanes_log2 >= 0 ? (uint32_t)ctx->sample_lanes_log2 : 3u);
+            // measured (profiles/r01b): 2..8 sample lanes x 16..4 adjacent pixels beat 32 lanes on one pixel by 2-4 % on a
+            // full frame, but a warp then carries 4x the work and the last warps of a launch run alone: the tail costs
+            // ~ 1/(lanes x pixels).  A small share of a frame (multi-GPU tiles) therefore takes more lanes per pixel:
+            // lanes x pixels >= 7 M  (profiles/r01e_tile_balance.txt: 1/8 of 1080p, 74 % -> 96 % of the ideal share).
+            uint32_t lS_auto = 3u;
+            while (lS_auto < 5u && ((uint64_t)A.n_my_tiles * 1024u << lS_auto) < (7ull << 20)) lS_auto++;
+            lS = std::min<uint32_t>(lS, ctx->sample_lanes_log2 >= 0 ? (uint32_t)ctx->sample_lanes_log2 : lS_auto);
             A.log2_sample_lanes = lS;
             // parked lanes before the BRDF code runs (variants with PT_F_DEFER): measured best 32 with textures, else 20
             A.shade_batch = ctx->shade_batch > 0 ? (uint32_t)ctx->shade_batch : ((ctx->features & PT_F_TEX) ? 32u : 20u);
