@@ -21,10 +21,15 @@ __host__ __device__ constexpr int pt_render_min_blocks(uint32_t F) {
 }
 
 // k_render / k_render_wf instantiations, from specialised to general: the first whose mask covers the scene runs
+#ifdef PT_DEFER_ALL          // experiment: shade deferral for every family (tools/build_variants.sh "128 8 -DPT_DEFER_ALL")
+#define PT_F_DEFER_X PT_F_DEFER
+#else
+#define PT_F_DEFER_X 0u
+#endif
 #define PT_RENDER_VARIANTS(X) \
-    X(PT_F_TEX | PT_F_LIGHT | PT_F_DEFER) X(PT_F_SPH_BVH | PT_F_LIGHT) X(PT_F_QUADS | PT_F_LIGHT) X(PT_F_SPH_BVH | PT_F_LENS) \
+    X(PT_F_TEX | PT_F_LIGHT | PT_F_DEFER) X(PT_F_SPH_BVH | PT_F_LIGHT | PT_F_DEFER) X(PT_F_QUADS | PT_F_LIGHT | PT_F_DEFER_X) X(PT_F_SPH_BVH | PT_F_LENS | PT_F_DEFER_X) \
     X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER) /* the same families with -d */ X(PT_F_TEX | PT_F_LIGHT | PT_F_DEFER | PT_F_LENS) \
-    X(PT_F_SPH_BVH | PT_F_LIGHT | PT_F_LENS) X(PT_F_QUADS | PT_F_LIGHT | PT_F_LENS) X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_LENS) \
+    X(PT_F_SPH_BVH | PT_F_LIGHT | PT_F_LENS | PT_F_DEFER) X(PT_F_QUADS | PT_F_LIGHT | PT_F_LENS | PT_F_DEFER_X) X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_LENS) \
     X(PT_F_ALL | PT_F_DEFER)
 
 #define PT_N_COUNTERS 72            // [0] rays [1] NaN retries [2] samples [3] -, then the PT_STATS_HIST experiment's histograms
@@ -134,8 +139,8 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
     // after the trace runs the longest straight-line code of the kernel at a third of the lanes.  With
     // PT_F_DEFER a lane that needs a BRDF sample PARKS in NEED_SHADE while the others keep regenerating
     // camera rays, until `shade_batch` lanes are parked (or nobody can regenerate); then the sampling code
-    // runs once for all of them.  Measured (profiles/r01d_sweep_defer.txt): w1 +18 %, w5 +8 %; it loses 3-5 %
-    // on w2/w3/w4, whose variants therefore shade at once.  The same deferral for the BVH walk lost everywhere.
+    // runs once for all of them.  Measured (profiles/r01d_sweep_defer.txt, r01e): w1 +18 %, w5 +8 %, w2 +7 %; it
+    // loses 2 % on w3/w4, whose variants therefore shade at once.  The same deferral for the BVH walk lost everywhere.
     // Scheduling never changes a sample's value: the Philox stream is keyed by (pixel, sample) and every
     // lane adds its own samples in order.
     enum { NO_RAY = 0, NEW_RAY = 1, NEED_SHADE = 2 };

@@ -3,6 +3,9 @@
 // hemisphere and emissive-sphere cone sampling with the reference's 50/50 estimator and pdf mixture --
 // every quirk of SURVEY.md Appendix A.6 kept, because the image oracle is the reference itself.
 #pragma once
+#ifndef PT_TEX_INLINE
+#define PT_TEX_INLINE __device__ __forceinline__
+#endif
 #include "pt_device.cuh"
 #include "pt_trace.cuh"
 
@@ -16,7 +19,7 @@ __device__ __forceinline__ float3 lerp3(float3 a, float3 b, float p) {
     float q = 1.0f - p;
     return f3(q * a.x + p * b.x, q * a.y + p * b.y, q * a.z + p * b.z);
 }
-__device__ __forceinline__ float3 pt_sample_texture(const PtTexture &t, float hx, float hy) {
+PT_TEX_INLINE float3 pt_sample_texture(const PtTexture &t, float hx, float hy) {
     float u = fabsf(hx * (float)t.w * 0.5f), v = fabsf(hy * (float)t.h * 0.5f);
     int x1 = (int)u, y1 = (int)v;
     float s = fminf(1.f, fmaxf(u - (float)x1, 0.f));
