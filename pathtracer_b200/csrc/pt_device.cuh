@@ -162,5 +162,6 @@ enum : uint32_t {
     PT_F_LIGHT = 32u,     // importance-sample spheres[0] (everything but PT_SCENE_JUST_COSINE)
     PT_F_ALL = 63u | 128u,
     PT_F_DEFER = 64u,     // kernel policy, not a scene feature: park lanes that need a BRDF sample (pt_kernels.cuh)
+    PT_F_QUEUE = 256u,    // kernel policy: BVH walks of a CTA are compacted through a shared-memory ray queue (pt_kernels.cuh)
     PT_F_LENS = 128u      // thin-lens camera (-d, always in world 4); pinhole-only variants drop that code
 };

@@ -21,14 +21,19 @@ __host__ __device__ constexpr int pt_render_min_blocks(uint32_t F) {
 }
 
 // k_render / k_render_wf instantiations, from specialised to general: the first whose mask covers the scene runs
+#ifdef PT_QUEUE_BVH          // experiment: CTA-level ray queue for the BVH walk
+#define PT_F_QUEUE_X PT_F_QUEUE
+#else
+#define PT_F_QUEUE_X 0u
+#endif
 #ifdef PT_DEFER_ALL          // experiment: shade deferral for every family (tools/build_variants.sh "128 8 -DPT_DEFER_ALL")
 #define PT_F_DEFER_X PT_F_DEFER
 #else
 #define PT_F_DEFER_X 0u
 #endif
 #define PT_RENDER_VARIANTS(X) \
-    X(PT_F_TEX | PT_F_LIGHT | PT_F_DEFER) X(PT_F_SPH_BVH | PT_F_LIGHT | PT_F_DEFER) X(PT_F_QUADS | PT_F_LIGHT | PT_F_DEFER_X) X(PT_F_SPH_BVH | PT_F_LENS | PT_F_DEFER_X) \
-    X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER) /* the same families with -d */ X(PT_F_TEX | PT_F_LIGHT | PT_F_DEFER | PT_F_LENS) \
+    X(PT_F_TEX | PT_F_LIGHT | PT_F_DEFER) X(PT_F_SPH_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_QUEUE_X) X(PT_F_QUADS | PT_F_LIGHT | PT_F_DEFER_X) X(PT_F_SPH_BVH | PT_F_LENS | PT_F_DEFER_X | PT_F_QUEUE_X) \
+    X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_QUEUE_X) /* the same families with -d */ X(PT_F_TEX | PT_F_LIGHT | PT_F_DEFER | PT_F_LENS) \
     X(PT_F_SPH_BVH | PT_F_LIGHT | PT_F_LENS | PT_F_DEFER) X(PT_F_QUADS | PT_F_LIGHT | PT_F_LENS | PT_F_DEFER_X) X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_LENS) \
     X(PT_F_ALL | PT_F_DEFER)
 
@@ -146,6 +151,19 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
     enum { NO_RAY = 0, NEW_RAY = 1, NEED_SHADE = 2 };
     uint32_t state = NO_RAY;
 
+    // PT_F_QUEUE: the BVH walks of the whole CTA go through a shared-memory ray queue.  Every lane does the cheap
+    // front end of the closest hit itself (linear lists + "does the ray enter the root?"); rays that enter are
+    // written to the queue at ballot/atomic-compacted slots, and after a barrier thread k walks ray k -- full warps
+    // however sparsely the rays were spread over the CTA's lanes -- and leaves (t, id) in the slot for the owner.
+    constexpr bool kQueue = (F & PT_F_QUEUE) && (((F & PT_F_SPH_BVH) != 0) != ((F & PT_F_TRI_BVH) != 0));
+    __shared__ float4 q_o[kQueue ? PT_RENDER_THREADS : 1], q_d[kQueue ? PT_RENDER_THREADS : 1];
+    __shared__ uint32_t q_n[2];
+    uint32_t q_iter = 0;
+    if (kQueue) {
+        if (threadIdx.x < 2) q_n[threadIdx.x] = 0;
+        __syncthreads();
+    }
+
     while (true) {
         if (state == NO_RAY && s < A.s_end) {
             pt_camera_ray<F>(S.cam, A.width, A.height, A.pp, A.pp_magic, x, y, s, retry, A.seed, rng, o, d);
@@ -155,7 +173,49 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
             state = NEW_RAY;
         }
         const uint32_t n_live = __popc(__ballot_sync(0xffffffffu, state != NO_RAY));
-        if (n_live == 0) break;
+        if (!kQueue && n_live == 0) break;
+
+        if (kQueue) {
+            bool deep = false;
+            if (state == NEW_RAY) {
+                h.t = 3.402823466e+38f;
+                h.id = PT_ID_MISS;
+                pt_hit_analytic<F>(S, o, d, pt_dot_exact(d), h);
+                deep = pt_bvh_root_hit((F & PT_F_TRI_BVH) ? S.tri_bvh : S.sphere_bvh, pt_ray_inv(o, d), h.t);
+            }
+            const uint32_t par = q_iter & 1u;
+            const uint32_t m = __ballot_sync(0xffffffffu, deep);
+            uint32_t slot = 0;
+            if (m != 0u) {
+                const int leader = __ffs((int)m) - 1;
+                if ((int)lane == leader) slot = atomicAdd(&q_n[par], (uint32_t)__popc(m));
+                slot = __shfl_sync(0xffffffffu, slot, leader) + __popc(m & ((1u << lane) - 1u));
+            }
+            if (deep) {
+                q_o[slot] = make_float4(o.x, o.y, o.z, h.t);
+                q_d[slot] = make_float4(d.x, d.y, d.z, __uint_as_float(h.id));
+            }
+            if (!__syncthreads_or(n_live != 0)) break;            // whole CTA finished
+            const uint32_t nq = q_n[par];
+            if (threadIdx.x == 0) q_n[par ^ 1u] = 0;
+            if (threadIdx.x < nq) {
+                const float4 qo = q_o[threadIdx.x], qd = q_d[threadIdx.x];
+                PtHit hh;
+                hh.t = qo.w;
+                hh.id = __float_as_uint(qd.w);
+                const float3 ro = f3(qo.x, qo.y, qo.z), rd = f3(qd.x, qd.y, qd.z);
+                if (F & PT_F_TRI_BVH) pt_bvh_walk<PT_LEAF_TRIS>(S, S.tri_bvh, ro, rd, pt_dot_exact(rd), hh);
+                else pt_bvh_walk<PT_LEAF_SPHERES>(S, S.sphere_bvh, ro, rd, pt_dot_exact(rd), hh);
+                q_o[threadIdx.x].w = hh.t;
+                q_d[threadIdx.x].w = __uint_as_float(hh.id);
+            }
+            __syncthreads();
+            if (deep) {
+                h.t = q_o[slot].w;
+                h.id = __float_as_uint(q_d[slot].w);
+            }
+            q_iter++;
+        }
 
         // ---- closest hit, emission, termination rules of RayCast (main.cpp:579-590, 799) ----
         bool done = false;
@@ -163,7 +223,7 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
 #ifdef PT_STATS_HIST
             g_pt_hist = A.counters;
 #endif
-            h = pt_closest_hit<F>(S, o, d);
+            if (!kQueue) h = pt_closest_hit<F>(S, o, d);
             n_rays++;
             float3 n;
             uint32_t mat;
