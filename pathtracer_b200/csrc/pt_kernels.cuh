@@ -131,7 +131,13 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
 
     uint32_t s = active ? A.s_begin + sl : A.s_end;
     uint32_t retry = 0, n_acc = 0, n_rays = 0, n_nan = 0;
-    float3 acc = f3(0, 0, 0);
+    // Per-pixel sums in a CANONICAL order, whatever the launch shape: sample s belongs to logical lane
+    // (s - s_begin) % 32; a physical lane owns 32/S logical lanes and keeps one accumulator for each (local
+    // memory, touched once per finished sample); at the end they are added in the order of a 32-lane xor
+    // butterfly.  So S = 8 (full frames) and S = 32 (small multi-GPU shares) give bit-identical pixels.
+    float accl[32][3];
+#pragma unroll 1
+    for (uint32_t k = 0; k < (32u >> lS); k++) accl[k][0] = accl[k][1] = accl[k][2] = 0.f;
     float3 o = f3(0, 0, 0), d = f3(0, 0, 1), beta = f3(1, 1, 1), L = f3(0, 0, 0);
     int depth = 0;
     PtHit h;
@@ -265,7 +271,10 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
                 n_nan++;
             } else {
                 if (isnan3(L)) L = f3(0, 0, 0);
-                acc = acc + L;
+                const uint32_t k = ((s - A.s_begin) >> lS) & ((32u >> lS) - 1u);
+                accl[k][0] += L.x;
+                accl[k][1] += L.y;
+                accl[k][2] += L.z;
                 n_acc++;
                 s += Sn;
                 retry = 0;
@@ -273,7 +282,17 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
         }
     }
 
-    // fixed-order tree sum over the S lanes of each pixel (deterministic for a given launch shape)
+    // the butterfly levels that pair logical lanes of the same physical lane (offsets 16 .. S) ...
+#pragma unroll 1
+    for (uint32_t ks = 16u >> lS; ks >= 1u; ks >>= 1)
+#pragma unroll 1
+        for (uint32_t k = 0; k < ks; k++) {
+            accl[k][0] += accl[k + ks][0];
+            accl[k][1] += accl[k + ks][1];
+            accl[k][2] += accl[k + ks][2];
+        }
+    float3 acc = f3(accl[0][0], accl[0][1], accl[0][2]);
+    // ... then the levels across the S lanes of each pixel (offsets S/2 .. 1)
     for (uint32_t off = Sn >> 1; off > 0; off >>= 1) {
         acc.x += __shfl_xor_sync(0xffffffffu, acc.x, off);
         acc.y += __shfl_xor_sync(0xffffffffu, acc.y, off);

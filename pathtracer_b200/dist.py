@@ -69,8 +69,8 @@ def gather_packed_tiles(packed, width, height, group=None):
     Returns the list of per-rank tensors on rank 0 (padded to the same length), else None."""
     import torch
     import torch.distributed as dist
-    world = dist.get_world_size(group)
-    rank = dist.get_rank(group)
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
     n_max = max_tiles_per_rank(width, height, world) * TILE * TILE
     if packed.numel() < n_max:
         packed = torch.cat([packed, packed.new_zeros(n_max - packed.numel())])
@@ -84,7 +84,7 @@ def gather_packed_tiles(packed, width, height, group=None):
 def reduce_accum(accum, group=None):
     """Sum the ranks' float accumulation buffers into rank 0's (in place)."""
     import torch.distributed as dist
-    if dist.get_world_size(group) > 1:
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
         dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM, group=group)
     return accum
 

@@ -89,10 +89,11 @@ def test_sample_sharding_sums_to_full_frame(core, worlds):
     assert st.samples == W * H * 36 and np.allclose(a2[..., :3], full[..., :3], rtol=2e-5, atol=1e-5)
 
 
-@pytest.mark.parametrize("lanes", [0, 1, 3, 5])
+@pytest.mark.parametrize("lanes", [0, 1, 2, 3, 4, 5])
 def test_launch_shape_does_not_change_the_samples(worlds, lanes, monkeypatch):
-    """S sample-lanes x P pixels per warp is a scheduling choice only: the per-pixel sums agree up to
-    float summation order and the sample counts are identical."""
+    """S sample-lanes x P pixels per warp is a scheduling choice only: the kernel adds a pixel's samples in a
+    canonical order (32 logical lanes, xor-butterfly), so every launch shape gives BIT-identical sums -- which is
+    what lets small multi-GPU shares use more lanes per pixel than a full frame and still reproduce it exactly."""
     W, H, pp = 100, 70, 6
     monkeypatch.setenv("PT_SAMPLE_LANES_LOG2", str(lanes))
     rc = render.RenderCore(0)
@@ -104,8 +105,7 @@ def test_launch_shape_does_not_change_the_samples(worlds, lanes, monkeypatch):
     rc2.upload_scene(worlds(5).scene(W, H))
     rc2.render(W, H, pp, seed=2)
     _, b, _ = rc2.readback(False, True)
-    assert np.array_equal(a[..., 3], b[..., 3])
-    assert np.allclose(a[..., :3], b[..., :3], rtol=1e-5, atol=1e-5)
+    assert np.array_equal(a, b)
     rc.close(); rc2.close()
 
 @pytest.mark.parametrize("w,lens", [(1, False), (2, False), (3, False), (4, False), (5, False), (3, True), (5, True)])
