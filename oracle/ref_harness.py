@@ -167,6 +167,18 @@ class RefHarness:
         self.lib.ref_random(n, _fp(out))
         return out
 
+    def aabb_test(self, o, d, origins, half_dims):
+        """RayIntersectWithAABB2 over boxes MakeAABB(origin, half_dim), nearest accepted as main.cpp:529-553."""
+        o = np.ascontiguousarray(o, np.float32).reshape(-1, 3)
+        d = np.ascontiguousarray(d, np.float32).reshape(-1, 3)
+        bo = np.ascontiguousarray(origins, np.float32).reshape(-1, 3)
+        bh = np.ascontiguousarray(half_dims, np.float32).reshape(-1, 3)
+        t = np.zeros(o.shape[0], np.float32)
+        idx = np.zeros(o.shape[0], np.int32)
+        face = np.zeros(o.shape[0], np.int32)
+        self.lib.ref_aabb_test(o.shape[0], _fp(o), _fp(d), bo.shape[0], _fp(bo), _fp(bh), _fp(t), _fp(idx), _fp(face))
+        return dict(t=t, index=idx, face=face)
+
     def sample_texture(self, idx, u, v):
         out = np.zeros(3, np.float32)
         self.lib.ref_sample_texture(idx, C.c_float(u), C.c_float(v), _fp(out))

@@ -415,6 +415,26 @@ void ref_sample_texture(int idx, float u, float v, float *rgb)
     rgb[0] = c.x; rgb[1] = c.y; rgb[2] = c.z;
 }
 
+/* the reference's box primitive (RayIntersectWithAABB2, ray_math.hpp:398-482, boxes from MakeAABB :484-492): none of
+   the five worlds holds one, so it is tapped directly.  Per ray: nearest accepted box as RayCastIntersect's loop does
+   (main.cpp:529-553): t > minHitDistance && t < best, in box order; outputs t (FLT_MAX = miss), box index, face. */
+void ref_aabb_test(int n_rays, const float *o, const float *d, int n_boxes, const float *origins, const float *half_dims,
+                   float *t_out, int *index_out, int *face_out)
+{
+    const float minHit = MIN_HIT_DISTANCE;
+    for (int r = 0; r < n_rays; r++) {
+        v3 ro = V3(o[3*r], o[3*r+1], o[3*r+2]), rd = V3(d[3*r], d[3*r+1], d[3*r+2]);
+        float best = FLT_MAX; int bi = -1, bf = -1;
+        for (int b = 0; b < n_boxes; b++) {
+            aabb_t box = MakeAABB(V3(origins[3*b], origins[3*b+1], origins[3*b+2]), V3(half_dims[3*b], half_dims[3*b+1], half_dims[3*b+2]));
+            bool early; int face = -1;
+            float t = RayIntersectWithAABB2(ro, rd, minHit, box, &early, &face);
+            if ((t > minHit) && (t < best)) { best = t; bi = b; bf = face; }
+        }
+        t_out[r] = best; index_out[r] = bi; face_out[r] = bf;
+    }
+}
+
 } /* extern "C" */
 
 #ifdef PT_REF_MAIN

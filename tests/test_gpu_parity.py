@@ -174,3 +174,35 @@ def test_image_within_monte_carlo_error_of_reference(core, worlds, name, w, lens
     assert abs(ref["med"] - null_med) < 0.2, (ref["med"], null_med)
     assert (np.abs(ref["g_z"]) < 5).all(), ref["g_z"]
     assert np.allclose(mu_gpu.mean((0, 1)), ref["mu"].mean((0, 1)), rtol=0.08)
+
+
+@pytest.mark.parametrize("seed,just_cosine,lens", [(11, False, False), (12, True, False), (13, False, True)])
+def test_synthetic_scene_with_boxes_vs_oracle(core, seed, just_cosine, lens):
+    """The primitives no built-in world holds -- axis-aligned boxes (main.cpp:529-553) -- next to quads, spheres and a
+    plane in one scene: closest-hit ids on rays from outside and inside the boxes, then whole renders on identical
+    Philox streams, against the oracle (itself bit-exact with the reference's box function, tests/golden/aabb.npz)."""
+    from synth import SynthScene
+    sc = SynthScene(seed=seed, just_cosine=just_cosine)
+    if lens:
+        sc.scene.camera.use_pinhole = 0
+    core.upload_scene(sc.scene)
+    o, d = sc.random_rays(40000, seed)
+    h = core.trace_rays(o, d)
+    r = O.intersect(sc.scene, o, d)
+    same = _ids_equal(h["kind"], h["index"], r["kind"], r["index"])
+    assert same.mean() >= 0.9995, f"{(~same).sum()} of {len(o)} ids differ"
+    assert (r["kind"] == 5).mean() > 0.2                       # boxes are what most rays hit
+    hit = same & (r["kind"] != 0)
+    assert np.abs(h["t"][hit] - r["t"][hit]).max() <= 2e-3 * r["t"][hit].max()
+    assert (h["mat"][same] == r["mat"][same]).all()
+    assert np.abs(h["normal"][same] - r["normal"][same]).max() < 1e-3
+    W, H, pp = sc.width, sc.height, 4
+    core.render(W, H, pp, seed=9)
+    bgra, acc, st = core.readback(True, True)
+    orc = O.render(sc.scene, W, H, pp, O.RNG_PHILOX, 9)
+    assert (acc[..., 3] == pp * pp).all()
+    gm, om = acc[..., :3] / (pp * pp), orc["sum"] / (pp * pp)
+    rel = np.abs(gm - om).max(2) / np.maximum(1e-2, np.abs(om).max(2))
+    assert (rel < 2e-3).mean() > 0.97, (rel < 2e-3).mean()
+    assert np.allclose(gm.mean((0, 1)), om.mean((0, 1)), rtol=1e-2)
+    assert (bgra == orc["ldr"]).mean() > 0.96

@@ -95,3 +95,23 @@ def test_philox_render_is_order_independent(worlds):
     assert np.allclose(a["sum"] + b["sum"], full["sum"], rtol=1e-12, atol=1e-12)
     sec, mf, ldr = O.render_threads(sc, 32, 18, 4, 7, threads=3)
     assert np.array_equal(mf, full["mean_f"]) and np.array_equal(ldr, full["ldr"])
+
+
+def test_aabb_primitive_bit_exact():
+    """RayIntersectWithAABB2 (ray_math.hpp:398-482) as a PRIMITIVE (main.cpp:529-553): no world has a box, so the
+    fixture comes from the reference function itself on a synthetic set of boxes (tools/make_golden.py --aabb):
+    rays from outside and inside, axis-parallel directions.  t, box index and face normal are bit-exact."""
+    from synth import FACE_NORMALS, SynthScene
+    g = golden("aabb.npz")
+    sc = SynthScene(seed=3, n_boxes=12, n_quads=0, n_spheres=0, plane=False)
+    assert np.array_equal(sc.box_origin, g["box_origin"]) and np.array_equal(sc.box_half, g["box_half"])
+    # drop the (required) light sphere out of the way: compare boxes only
+    sc.spheres["p"][0] = (0, 0, 5000.0)
+    h = O.intersect(sc.scene, g["o"], g["d"])
+    hit = g["index"] >= 0
+    assert hit.sum() > 5000 and (~hit).sum() > 5000
+    box = h["kind"] == 5
+    assert np.array_equal(box, hit)
+    assert np.array_equal(h["t"][hit], g["t"][hit]) and np.array_equal(h["index"][hit], g["index"][hit])
+    assert np.array_equal(h["normal"][hit], FACE_NORMALS[g["face"][hit]])
+    assert np.array_equal(h["mat"][hit], sc.aabbs["mat"][g["index"][hit]])

@@ -80,5 +80,20 @@ def main():
     print("golden bytes:", total)
 
 
+def make_aabb_fixture():
+    """The box primitive (no world holds one): the reference's RayIntersectWithAABB2 over MakeAABB boxes, nearest
+    accepted box per ray as RayCastIntersect's loop does (main.cpp:529-553) -> tests/golden/aabb.npz."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from synth import SynthScene
+    sc = SynthScene(seed=3, n_boxes=12, n_quads=0, n_spheres=0, plane=False)
+    o, d = sc.random_rays(30000, seed=5)
+    r = RefHarness().aabb_test(o, d, sc.box_origin, sc.box_half)
+    np.savez_compressed(os.path.join(OUT, "aabb.npz"), o=o, d=d, box_origin=sc.box_origin, box_half=sc.box_half,
+                        t=r["t"], index=r["index"], face=r["face"])
+    print("aabb.npz: hits", int((r["index"] >= 0).sum()), "of", len(o))
+
+
 if __name__ == "__main__":
-    main()
+    if "--aabb" not in sys.argv:          # --aabb: only (re)write the box fixture
+        main()
+    make_aabb_fixture()
