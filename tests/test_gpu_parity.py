@@ -206,3 +206,35 @@ def test_synthetic_scene_with_boxes_vs_oracle(core, seed, just_cosine, lens):
     assert (rel < 2e-3).mean() > 0.97, (rel < 2e-3).mean()
     assert np.allclose(gm.mean((0, 1)), om.mean((0, 1)), rtol=1e-2)
     assert (bgra == orc["ldr"]).mean() > 0.96
+
+
+def _legacy_similarity(a, b):
+    """The reference's ImageCompare metric on BGRA words (src/image_compare.c:79-134; red ignored, alpha twice)."""
+    ab, bb = a.view(np.uint8).reshape(a.shape + (4,)).astype(np.float64), b.view(np.uint8).reshape(b.shape + (4,)).astype(np.float64)
+    d = (ab - bb) / 255.0
+    return float((1.0 - np.sqrt(2 * d[..., 3] ** 2 + d[..., 0] ** 2 + d[..., 1] ** 2)).mean() * 100.0)
+
+
+def _rmse(a, b):
+    ab, bb = a.view(np.uint8).reshape(a.shape + (4,))[..., :3].astype(np.float64), b.view(np.uint8).reshape(b.shape + (4,))[..., :3].astype(np.float64)
+    return float(np.sqrt(((ab - bb) ** 2).mean()))
+
+
+@pytest.mark.parametrize("w,pp", [(3, 8), (5, 8)])
+def test_ldr_image_within_the_references_own_noise_floor(core, worlds, w, pp):
+    """the 8-bit image the user sees.  Two independent renders by the reference's estimator (the oracle
+    in mt19937 mode, bit-exact with the reference) differ by Monte-Carlo noise; the GPU image must be as close to
+    either of them as they are to each other, in the reference's own "Percentage Similarity" and in RMSE."""
+    W, H = 160, 90
+    sc = worlds(w).scene(W, H)
+    refs = []
+    for seed in (31, 32):
+        O.seed_mt(seed)
+        refs.append(O.render(sc, W, H, pp, O.RNG_MT19937)["ldr"])
+    core.upload_scene(sc)
+    core.render(W, H, pp, seed=5)
+    gpu, _, _ = core.readback(True, False)
+    floor_sim, floor_rmse = _legacy_similarity(refs[0], refs[1]), _rmse(refs[0], refs[1])
+    for r in refs:
+        assert _legacy_similarity(gpu, r) >= floor_sim - 0.4, (_legacy_similarity(gpu, r), floor_sim)
+        assert _rmse(gpu, r) <= floor_rmse * 1.08 + 0.2, (_rmse(gpu, r), floor_rmse)
