@@ -350,7 +350,13 @@ extern "C" int pt_upload_scene(pt_context *ctx, const pt_scene *s) {
         ctx->bvh_nodes += D.tri_bvh.n_nodes; ctx->bvh_prims += D.tri_bvh.n_prims;
     }
 
-    // --- textures (RGBA8 as given) ---
+    // --- textures (RGBA8 as given) + the byte -> [0,1] table ---
+    const float *d_unit255 = nullptr;
+    {
+        std::vector<float> lut(256);
+        for (int i = 0; i < 256; i++) lut[i] = (float)i / 255.f;          // IEEE division, as LoadTexture does per texel
+        if ((rc = upload(ctx, lut, &d_unit255))) return rc;
+    }
     for (int i = 0; i < 4; i++) {
         const pt_texture &t = s->textures[i];
         if (!t.rgba8 || t.width <= 0 || t.height <= 0) continue;
@@ -361,6 +367,9 @@ extern "C" int pt_upload_scene(pt_context *ctx, const pt_scene *s) {
         CK(cudaMemcpyAsync(p, t.rgba8, bytes, cudaMemcpyHostToDevice, ctx->stream));
         D.tex[i].texels = (const uchar4 *)p;
         D.tex[i].w = t.width; D.tex[i].h = t.height;
+        D.tex[i].unit255 = d_unit255;
+        D.tex[i].wmask = (t.width > 1 && (t.width & (t.width - 1)) == 0) ? t.width - 1 : 0;
+        D.tex[i].hmask = (t.height > 1 && (t.height & (t.height - 1)) == 0) ? t.height - 1 : 0;
     }
     for (uint32_t m = 0; m < s->n_materials; m++) {
         const pt_material &mm = s->materials[m];

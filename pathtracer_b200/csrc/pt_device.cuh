@@ -44,7 +44,9 @@ struct PtBvh {
 
 struct PtTexture {
     const uchar4 *texels;     // RGBA8, row-major
+    const float *unit255;     // 256 floats: (float)i / 255.f computed by IEEE division on the host (main.cpp:1737-1739)
     int w, h;
+    int wmask, hmask;         // w-1 / h-1 when a power of two (x % w == x & mask), else 0
 };
 
 // everything the kernels read; passed by value as a __grid_constant__ kernel parameter

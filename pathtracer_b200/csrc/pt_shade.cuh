@@ -13,7 +13,9 @@
 // modulo size, bilinear on texels = byte/255 (main.cpp:1737-1739).  Only mip 0 is ever read.
 __device__ __forceinline__ float3 pt_texel(const PtTexture &t, int x, int y) {
     uchar4 p = __ldg(t.texels + (size_t)y * t.w + x);
-    return f3((float)p.x / 255.f, (float)p.y / 255.f, (float)p.z / 255.f);     // IEEE division: bit-identical texels
+    // byte / 255.f must be the IEEE quotient (bit-identical texels); 12 divisions per bilinear fetch were 10 % of
+    // the w1 kernel's instructions, so the 256 quotients come from a table the host filled with the same division
+    return f3(__ldg(t.unit255 + p.x), __ldg(t.unit255 + p.y), __ldg(t.unit255 + p.z));
 }
 __device__ __forceinline__ float3 lerp3(float3 a, float3 b, float p) {
     float q = 1.0f - p;
@@ -24,10 +26,10 @@ PT_TEX_INLINE float3 pt_sample_texture(const PtTexture &t, float hx, float hy) {
     int x1 = (int)u, y1 = (int)v;
     float s = fminf(1.f, fmaxf(u - (float)x1, 0.f));
     float tt = fminf(1.f, fmaxf(v - (float)y1, 0.f));
-    x1 = x1 % t.w;
-    int x2 = (x1 + 1) % t.w;
-    y1 = y1 % t.h;
-    int y2 = (y1 + 1) % t.h;
+    x1 = t.wmask ? (x1 & t.wmask) : (x1 % t.w);
+    y1 = t.hmask ? (y1 & t.hmask) : (y1 % t.h);
+    int x2 = x1 + 1 == t.w ? 0 : x1 + 1;
+    int y2 = y1 + 1 == t.h ? 0 : y1 + 1;
     float3 top = lerp3(pt_texel(t, x1, y1), pt_texel(t, x2, y1), s);
     float3 bot = lerp3(pt_texel(t, x1, y2), pt_texel(t, x2, y2), s);
     return lerp3(top, bot, tt);
