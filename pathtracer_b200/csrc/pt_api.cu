@@ -47,6 +47,8 @@ struct pt_context {
     uint32_t bvh_nodes = 0, bvh_prims = 0;
     PtWavefront wf;
     int sample_lanes_log2 = -1;                // -1 = auto
+    bool sah_sweep = true;                     // PT_SAH_SWEEP=0: 16-bin SAH everywhere (experiment)
+    int tri_leaf = 4, sph_leaf = 2;            // max primitives per BVH leaf (PT_TRI_LEAF / PT_SPH_LEAF; measured, profiles/r01f)
     int shade_batch = 0;                       // PT_SHADE_BATCH: deferral threshold of k_render (0 = per-variant default)
     // single-process multi-GPU (pt_gather_tiles_from / pt_add_accum_from)
     void *pack_buf = nullptr, *stage_buf = nullptr;
@@ -107,6 +109,9 @@ extern "C" int pt_create(const pt_config *cfg, pt_context **out) {
     cudaMemset(ctx->counters, 0, PT_N_COUNTERS * sizeof(unsigned long long));
     if (const char *s = getenv("PT_SAMPLE_LANES_LOG2")) ctx->sample_lanes_log2 = atoi(s);
     if (const char *s = getenv("PT_SHADE_BATCH")) ctx->shade_batch = atoi(s);
+    if (const char *s = getenv("PT_SAH_SWEEP")) ctx->sah_sweep = atoi(s) != 0;
+    if (const char *s = getenv("PT_TRI_LEAF")) ctx->tri_leaf = std::max(1, std::min(64, atoi(s)));
+    if (const char *s = getenv("PT_SPH_LEAF")) ctx->sph_leaf = std::max(1, std::min(64, atoi(s)));
     if (const char *s = getenv("PT_WF_PIXELS_LOG2")) ctx->wf.pixels_log2 = atoi(s);
     if (const char *s = getenv("PT_KERNEL")) {          // experiments: overrides pt_config.kernel
         if (!strcmp(s, "mega")) ctx->kernel = PT_KERNEL_MEGA;
@@ -296,8 +301,8 @@ extern "C" int pt_upload_scene(pt_context *ctx, const pt_scene *s) {
             boxes[i].mx[0] = q.x + q.w; boxes[i].mx[1] = q.y + q.w; boxes[i].mx[2] = q.z + q.w;
         }
         ptbvh::Result r;
-        if (ctx->bvh_builder == PT_BVH_DEVICE_LBVH) { if ((rc = pt_lbvh_build(ctx->stream, boxes, 2, r, ctx->error))) return rc; }
-        else r = ptbvh::Builder(boxes, 2).build();
+        if (ctx->bvh_builder == PT_BVH_DEVICE_LBVH) { if ((rc = pt_lbvh_build(ctx->stream, boxes, ctx->sph_leaf, r, ctx->error))) return rc; }
+        else r = ptbvh::Builder(boxes, ctx->sph_leaf, ctx->sah_sweep).build();
         if (r.max_depth > PT_STACK_DEPTH - 2) return fail(ctx, PT_ERR_UNSUPPORTED, "sphere BVH deeper than the traversal stack");
         std::vector<float4> ordered(r.order.size());
         std::vector<uint32_t> ids(r.order.size());
@@ -339,8 +344,8 @@ extern "C" int pt_upload_scene(pt_context *ctx, const pt_scene *s) {
             normals[i] = make_float4(recs[i].r0.x, recs[i].r0.y, recs[i].r0.z, 0.f);
         }
         ptbvh::Result r;
-        if (ctx->bvh_builder == PT_BVH_DEVICE_LBVH) { if ((rc = pt_lbvh_build(ctx->stream, boxes, 4, r, ctx->error))) return rc; }
-        else r = ptbvh::Builder(boxes, 4).build();
+        if (ctx->bvh_builder == PT_BVH_DEVICE_LBVH) { if ((rc = pt_lbvh_build(ctx->stream, boxes, ctx->tri_leaf, r, ctx->error))) return rc; }
+        else r = ptbvh::Builder(boxes, ctx->tri_leaf, ctx->sah_sweep).build();
         if (r.max_depth > PT_STACK_DEPTH - 2) return fail(ctx, PT_ERR_UNSUPPORTED, "triangle BVH deeper than the traversal stack");
         std::vector<PtPlanar> ordered(r.order.size());
         for (size_t i = 0; i < r.order.size(); i++) ordered[i] = recs[r.order[i]];

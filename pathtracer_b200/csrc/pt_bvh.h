@@ -42,7 +42,7 @@ inline void store_child_box(Node &n, int side, const Box &b) {
 
 class Builder {
 public:
-    Builder(const std::vector<Box> &prim_boxes, int max_leaf) : boxes_(prim_boxes), max_leaf_(max_leaf) {
+    Builder(const std::vector<Box> &prim_boxes, int max_leaf, bool sweep = true) : boxes_(prim_boxes), max_leaf_(max_leaf), sweep_(sweep) {
         cent_.resize(boxes_.size() * 3);
         for (size_t i = 0; i < boxes_.size(); i++)
             for (int k = 0; k < 3; k++) cent_[3 * i + k] = 0.5f * (boxes_[i].mn[k] + boxes_[i].mx[k]);
@@ -90,8 +90,32 @@ private:
         return b;
     }
 
+    // exact sweep SAH for small ranges: sort by centroid on each axis and evaluate every split position
+    uint32_t partition_sweep(uint32_t first, uint32_t last) {
+        const uint32_t n = last - first;
+        float best_cost = FLT_MAX; int best_axis = -1; uint32_t best_k = 0;
+        std::vector<uint32_t> idx(n), best_order;
+        std::vector<float> right_area(n);
+        for (int ax = 0; ax < 3; ax++) {
+            for (uint32_t i = 0; i < n; i++) idx[i] = out_->order[first + i];
+            std::stable_sort(idx.begin(), idx.end(), [&](uint32_t a, uint32_t b) { return cent_[3 * a + ax] < cent_[3 * b + ax]; });
+            Box acc; acc.reset();
+            for (uint32_t i = n; i-- > 1;) { acc.grow(boxes_[idx[i]]); right_area[i] = acc.area(); }
+            acc.reset();
+            for (uint32_t k = 1; k < n; k++) {                 // left = idx[0..k), right = idx[k..n)
+                acc.grow(boxes_[idx[k - 1]]);
+                float cost = acc.area() * (float)k + right_area[k] * (float)(n - k);
+                if (cost < best_cost) { best_cost = cost; best_axis = ax; best_k = k; best_order = idx; }
+            }
+        }
+        if (best_axis < 0) return first + n / 2;
+        for (uint32_t i = 0; i < n; i++) out_->order[first + i] = best_order[i];
+        return first + best_k;
+    }
+
     // chooses the split of [first,last) and returns mid; falls back to a median split when SAH finds nothing
     uint32_t partition(uint32_t first, uint32_t last) {
+        if (sweep_ && last - first <= 4096) return partition_sweep(first, last);
         const int NB = 16;
         Box cb; cb.reset();
         for (uint32_t i = first; i < last; i++) cb.grow(&cent_[3 * out_->order[i]]);
@@ -165,6 +189,7 @@ private:
     const std::vector<Box> &boxes_;
     std::vector<float> cent_;
     int max_leaf_;
+    bool sweep_ = true;       // exact SAH below 4096 primitives per range, 16 bins above
     Result *out_ = nullptr;
 };
 

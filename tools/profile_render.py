@@ -13,9 +13,10 @@ ap.add_argument("--height", type=int, default=1080)
 ap.add_argument("--pp", type=int, default=8)
 ap.add_argument("--frames", type=int, default=2)
 ap.add_argument("--kernel", default="auto")
+ap.add_argument("--bvh", default="sah", choices=["sah", "lbvh"])
 a = ap.parse_args()
 k = {"auto": T.KERNEL_AUTO, "mega": T.KERNEL_MEGA, "wavefront": T.KERNEL_WAVEFRONT}[a.kernel]
-rc = render.RenderCore(0, kernel=k)
+rc = render.RenderCore(0, bvh=T.BVH_DEVICE_LBVH if a.bvh == 'lbvh' else T.BVH_HOST_SAH, kernel=k)
 rc.upload_scene(host.HostWorld(a.world).scene(a.width, a.height))
 for i in range(a.frames):
     rc.render(a.width, a.height, a.pp, seed=1 + i)
