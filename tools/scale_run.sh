@@ -3,8 +3,8 @@
 out=${1:-gpurun_out/scale.jsonl}; shift
 : > $out
 for n in 1 2 4 8; do
-  if [ $n -eq 1 ]; then python bench.py --gpus 1 --steps 5 --warmup 3 --no-cpu-baseline "$@" | tail -1 >> $out
-  else python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $((29600+n)) bench.py --gpus $n --steps 5 --warmup 3 "$@" 2>/dev/null | tail -1 >> $out; fi
+  if [ $n -eq 1 ]; then python bench.py --gpus 1 --steps ${STEPS:-5} --warmup 3 --no-cpu-baseline "$@" | tail -1 >> $out
+  else python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $((29600+n)) bench.py --gpus $n --steps ${STEPS:-5} --warmup 3 "$@" 2>/dev/null | tail -1 >> $out; fi
 done
 python - "$out" <<'PY'
 import json, sys
