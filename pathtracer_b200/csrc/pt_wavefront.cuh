@@ -40,6 +40,8 @@ enum { WF_OX, WF_OY, WF_OZ, WF_DX, WF_DY, WF_DZ, WF_BX, WF_BY, WF_BZ, WF_LX, WF_
 enum { WF_BVH = 0, WF_END = 1, WF_SHADE = 2, WF_HIT = 3, WF_NONE = 4 };
 #define WF_FRESH (1u << 24)      // misc: depth | retry << 8 | philox block << 16 | WF_FRESH
 
+static_assert(PT_WF_POOL >= 32 && PT_WF_POOL <= 256 && (PT_WF_POOL & (PT_WF_POOL - 1)) == 0, "PT_WF_POOL: power of two in [32, 256] (8-bit list entries)");
+
 struct PtWfWarp {                                  // shared memory of one warp: SoA, field-major
     float f[WF_FIELDS][PT_WF_POOL];                // path p of field k at bank (p % 32): <= POOL/32-way conflicts
     uint8_t list[4][PT_WF_POOL];
