@@ -113,8 +113,13 @@ typedef struct pt_scene {
     pt_camera          camera;
 } pt_scene;
 
-enum { PT_BVH_HOST_SAH = 0, PT_BVH_DEVICE_LBVH = 1 };
-enum { PT_KERNEL_AUTO = 0, PT_KERNEL_MEGA = 1, PT_KERNEL_WAVEFRONT = 2 };
+/* BVH builder (replaces GenerateAccelerationStructure, main.cpp:1188-1452); both give bit-identical images */
+enum { PT_BVH_HOST_SAH = 0,       /* surface-area heuristic on the host (default; best traversal) */
+       PT_BVH_DEVICE_LBVH = 1 };  /* Morton codes -> radix sort -> Karras hierarchy -> refit, on the GPU */
+/* render kernel; both run the same samples (Philox streams keyed by pixel and sample) */
+enum { PT_KERNEL_AUTO = 0,        /* = PT_KERNEL_MEGA */
+       PT_KERNEL_MEGA = 1,        /* path-regeneration megakernel, feature-specialised variants (default) */
+       PT_KERNEL_WAVEFRONT = 2 }; /* paths pooled in shared memory, one index list per stage, per warp */
 
 typedef struct pt_config {
     uint32_t struct_size;     /* = sizeof(pt_config) */
