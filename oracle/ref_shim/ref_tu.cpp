@@ -437,6 +437,89 @@ void ref_aabb_test(int n_rays, const float *o, const float *d, int n_boxes, cons
 
 } /* extern "C" */
 
+#ifdef PT_REF_B200
+/* ------------------------------------------------------------------------- */
+/* pathtracer_ref_b200: THE DROP-IN, demonstrated.  The reference program -- its ParseArgs, LoadWorld,     */
+/* GLB/texture loaders, DefineCamera and WriteDIBImage, compiled unmodified above -- with ONE routine      */
+/* substituted: the thread shim hands CreateThread(MasterThread) (main.cpp:239-246) this function instead, */
+/* which is the patch of INTEGRATION.md section 1 verbatim: g_world/g_camera/g_textures -> pt_upload_scene  */
+/* -> pt_render -> pt_readback into g_image.pixelPointer, then the reference's own tail (main.cpp:983-986). */
+/* Extra knob: PT_SEED=n (the reference seeds from random_device).                                         */
+/* ------------------------------------------------------------------------- */
+#include "pt_api.h"
+
+static DWORD WINAPI MasterThread_b200(LPVOID)
+{
+    static_assert(sizeof(material_t) == sizeof(pt_material) && sizeof(sphere_t) == sizeof(pt_sphere) &&
+                  sizeof(plane_t) == sizeof(pt_plane) && sizeof(ref_quad_t) == sizeof(pt_quad) &&
+                  sizeof(aabb_t) == sizeof(pt_aabb) && sizeof(camera_t) == sizeof(pt_camera), "pt_api.h mirrors ray.hpp");
+
+    pt_config cfg = { sizeof(pt_config), /*device*/0, PT_BVH_HOST_SAH, PT_KERNEL_AUTO, /*stream*/nullptr };
+    pt_context *pt = nullptr;
+    if (pt_create(&cfg, &pt) != PT_OK) { fprintf(stderr, "pt: %s\n", pt_last_error(nullptr)); exit(1); }
+
+    pt_scene sc = {};
+    sc.struct_size = sizeof(pt_scene);
+    sc.flags = (g_bNormals ? PT_SCENE_NORMAL_MAPS : 0) | (g_bMetalness ? PT_SCENE_METALNESS_MAPS : 0) |
+               (g_bRoughness ? PT_SCENE_ROUGHNESS_MAPS : 0) |
+               (g_worldKind == WORLD_RAYTRACING_ONE_WEEKEND ? PT_SCENE_JUST_COSINE : 0);      /* main.cpp:654-655 */
+    sc.n_materials = nc_sbcount(g_world.materials);  sc.materials = (const pt_material *)g_world.materials;
+    sc.n_spheres   = nc_sbcount(g_world.spheres);    sc.spheres   = (const pt_sphere *)g_world.spheres;
+    sc.n_planes    = nc_sbcount(g_world.planes);     sc.planes    = (const pt_plane *)g_world.planes;
+    sc.n_quads     = nc_sbcount(g_world.quads);      sc.quads     = (const pt_quad *)g_world.quads;
+    sc.n_aabbs     = nc_sbcount(g_world.aabbs);      sc.aabbs     = (const pt_aabb *)g_world.aabbs;
+
+    /* meshes[0] only (main.cpp:483): 3 consecutive v3 per triangle, material = that of its first vertex (main.cpp:520) */
+    int *triMat = nullptr;
+    if (nc_sbcount(g_world.meshes)) {
+        mesh_t &m = g_world.meshes[0];
+        sc.n_triangles = m.pointCount / 3;
+        sc.tri_points  = (const float *)m.points;
+        triMat = (int *)malloc(sizeof(int) * (sc.n_triangles ? sc.n_triangles : 1));
+        for (unsigned t = 0; t < sc.n_triangles; t++) triMat[t] = m.matIndices[3 * t];
+        sc.tri_materials = triMat;
+    }
+
+    /* g_textures[i].mips[0] holds float3 = byte/255.f (main.cpp:1737-1739); the library wants the bytes back */
+    unsigned char *texBytes[4] = {};
+    for (int i = 0; i < 4; i++) if (g_textures[i].mips && g_textures[i].mips[0].data) {
+        texture_t t = g_textures[i].mips[0];
+        size_t n = (size_t)t.width * t.height;
+        texBytes[i] = (unsigned char *)malloc(n * 4);
+        for (size_t p = 0; p < n; p++) {
+            texBytes[i][4*p+0] = (unsigned char)(t.data[p].x * 255.f + 0.5f);
+            texBytes[i][4*p+1] = (unsigned char)(t.data[p].y * 255.f + 0.5f);
+            texBytes[i][4*p+2] = (unsigned char)(t.data[p].z * 255.f + 0.5f);
+            texBytes[i][4*p+3] = 255;
+        }
+        sc.textures[i].width = t.width; sc.textures[i].height = t.height;
+        sc.textures[i].rgba8 = texBytes[i];
+    }
+    memcpy(&sc.camera, &g_camera, sizeof(pt_camera));             /* camera_t, ray.hpp:176-186: same field order */
+
+    int rc = pt_upload_scene(pt, &sc);                            /* copies: host pointers may go */
+    for (int i = 0; i < 4; i++) free(texBytes[i]);
+    free(triMat);
+
+    pt_render_params rp = {};
+    rp.struct_size = sizeof(rp);
+    rp.width = g_image.width; rp.height = g_image.height;
+    rp.pp = g_pp;                                                  /* main.cpp:113 */
+    rp.seed = getenv("PT_SEED") ? strtoull(getenv("PT_SEED"), nullptr, 10) : (uint64_t)std::random_device{}();
+    rp.flags = PT_RENDER_CLEAR;
+    if (rc == PT_OK) rc = pt_render(pt, &rp);
+    if (rc == PT_OK) rc = pt_readback(pt, (uint32_t *)g_image.pixelPointer, nullptr, nullptr);   /* row 0 = bottom */
+    if (rc != PT_OK) { fprintf(stderr, "pt: %s\n", pt_last_error(pt)); exit(1); }
+    pt_destroy(pt);
+
+    WriteDIBImage(g_image, "test.bmp");                            /* main.cpp:983-986 */
+    printf("Done. Image written to test.bmp.\n");
+    ExitThread(0);
+}
+
+static LPTHREAD_START_ROUTINE b200_thread_hook(LPTHREAD_START_ROUTINE fn) { return fn == MasterThread ? MasterThread_b200 : fn; }
+#endif
+
 #ifdef PT_REF_MAIN
 /* pathtracer_ref: the reference program, CLI and all (ParseArgs -> ... -> test.bmp).
    Extra environment knobs of the shim only: PT_REF_SIZE=WxH, PT_REF_SEED=n, PT_REF_CORES=n. */
@@ -447,6 +530,9 @@ int main(int argc, char **argv)
     mallopt(M_MMAP_THRESHOLD, 1 << 20);   /* see ref_load */
     if (const char *s = getenv("PT_REF_SEED")) ref_seed((unsigned)strtoul(s, nullptr, 10));
     if (const char *s = getenv("PT_REF_CORES")) pt_shim_core_count = atoi(s);
+#ifdef PT_REF_B200
+    pt_shim_thread_hook = b200_thread_hook;
+#endif
     int rc = ref_main();
     if (pt_shim_first_worker_ns && pt_shim_last_join_ns) {
         double sec = (double)(pt_shim_last_join_ns - pt_shim_first_worker_ns) * 1e-9;

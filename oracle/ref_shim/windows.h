@@ -74,8 +74,14 @@ static void *pt_shim_trampoline(void *p) {
     return nullptr;
 }
 
+/* drop-in demo (pathtracer_ref_b200): lets the wrapper TU substitute one thread routine -- the reference's
+   MasterThread -- without touching the reference's source */
+typedef LPTHREAD_START_ROUTINE (*pt_shim_thread_hook_t)(LPTHREAD_START_ROUTINE);
+static pt_shim_thread_hook_t pt_shim_thread_hook = nullptr;
+
 static inline HANDLE CreateThread(void *, size_t, LPTHREAD_START_ROUTINE fn, LPVOID arg, DWORD, void *) {
     pt_shim_thread *t = new pt_shim_thread();
+    if (pt_shim_thread_hook) fn = pt_shim_thread_hook(fn);
     t->fn = fn;
     t->arg = arg;
     t->done.store(0);

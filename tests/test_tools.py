@@ -109,3 +109,26 @@ def test_cli_fails_loudly(tmp_path):
         pytest.skip("bin/pathtracer not built")
     r = subprocess.run([exe, "-w5", "-p1", "--res", str(tmp_path / "nowhere")], capture_output=True, text=True, cwd=str(tmp_path))
     assert r.returncode != 0 and "cannot build world 5" in r.stderr
+
+
+# ---- the drop-in itself: the reference program with MasterThread handed to the library ----------
+@pytest.mark.gpu
+@pytest.mark.parametrize("w,extra", [(5, []), (1, []), (3, ["-d"]), (4, [])])
+def test_reference_program_with_the_library_dropped_in(worlds, core, w, extra):
+    """oracle/_ref/pathtracer_ref_b200 = the UNMODIFIED reference program (its ParseArgs, LoadWorld, GLB and texture
+    loaders, DefineCamera, WriteDIBImage) where the thread shim substitutes MasterThread by the INTEGRATION.md patch
+    (g_world / g_camera / g_textures -> pt_upload_scene -> pt_render -> pt_readback into g_image).  Its test.bmp must
+    be byte-identical to what the repo's own host + the same library produce for the same seed."""
+    exe = os.path.join(ROOT, "oracle", "_ref", "pathtracer_ref_b200")
+    run = os.path.join(ROOT, "oracle", "_ref", "run")
+    if not (os.path.exists(exe) and os.path.isdir(run)):
+        pytest.skip("oracle/_ref/pathtracer_ref_b200 not built (needs /root/reference and libpt_b200.so)")
+    W, H, pp = 160, 96, 4
+    env = dict(os.environ, PT_REF_SIZE=f"{W}x{H}", PT_SEED="5", PT_REF_SEED="7")     # PT_REF_SEED: world 4's layout
+    r = subprocess.run([exe, f"-w{w}", f"-p{pp}", *extra], cwd=run, env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "Done. Image written to test.bmp." in r.stdout, r.stderr[-500:]
+    got = host.read_bmp(os.path.join(run, "test.bmp"))
+    core.upload_scene(worlds(w).scene(W, H, lens=bool(extra)))
+    core.render(W, H, pp, seed=5)
+    want, _, _ = core.readback(True, False)
+    assert got.shape == want.shape and np.array_equal(got, want)
