@@ -11,6 +11,7 @@
 
 #include "pt_api.h"
 #include "pt_bvh.h"
+#include "pt_cluster.h"
 #include "pt_device.cuh"
 #include "pt_kernels.cuh"
 #include "pt_lbvh.cuh"
@@ -50,6 +51,7 @@ struct pt_context {
     bool sah_sweep = true;                     // PT_SAH_SWEEP=0: 16-bin SAH everywhere (experiment)
     int tri_leaf = 4, sph_leaf = 2;            // max primitives per BVH leaf (PT_TRI_LEAF / PT_SPH_LEAF; measured, profiles/r01f)
     int shade_batch = 0;                       // PT_SHADE_BATCH: deferral threshold of k_render (0 = per-variant default)
+    int coop_max = 0;                          // PT_COOP_MAX: walks entered by <= this many lanes of a warp are traced cooperatively (0 = off)
     // single-process multi-GPU (pt_gather_tiles_from / pt_add_accum_from)
     void *pack_buf = nullptr, *stage_buf = nullptr;
     size_t pack_bytes = 0, stage_bytes = 0;
@@ -109,6 +111,7 @@ extern "C" int pt_create(const pt_config *cfg, pt_context **out) {
     cudaMemset(ctx->counters, 0, PT_N_COUNTERS * sizeof(unsigned long long));
     if (const char *s = getenv("PT_SAMPLE_LANES_LOG2")) ctx->sample_lanes_log2 = atoi(s);
     if (const char *s = getenv("PT_SHADE_BATCH")) ctx->shade_batch = atoi(s);
+    if (const char *s = getenv("PT_COOP_MAX")) ctx->coop_max = std::max(0, std::min(32, atoi(s)));
     if (const char *s = getenv("PT_SAH_SWEEP")) ctx->sah_sweep = atoi(s) != 0;
     if (const char *s = getenv("PT_TRI_LEAF")) ctx->tri_leaf = std::max(1, std::min(64, atoi(s)));
     if (const char *s = getenv("PT_SPH_LEAF")) ctx->sph_leaf = std::max(1, std::min(64, atoi(s)));
@@ -198,6 +201,21 @@ static PtPlanar make_planar(const float *A, const float *u, const float *v) {
     return r;
 }
 
+// the <= 32-cluster cut of a tree for the PT_F_COOP variants; *out stays NULL when the tree has no such cut
+static int upload_clusters(pt_context *ctx, const ptbvh::Result &r, const float4 **out, uint32_t *n_out) {
+    *out = nullptr; *n_out = 0;
+    if (ctx->coop_max <= 0) return PT_OK;
+    const ptbvh::ClusterCut cut = ptbvh::build_cut(r);
+    if (cut.clusters.empty()) return PT_OK;
+    const std::vector<float> img = cut.image();
+    std::vector<float4> v(2 * ptbvh::kClusterLanes);
+    memcpy(v.data(), img.data(), v.size() * sizeof(float4));
+    int rc = upload(ctx, v, out);
+    if (rc) return rc;
+    *n_out = (uint32_t)cut.clusters.size();
+    return PT_OK;
+}
+
 static int upload_bvh(pt_context *ctx, const ptbvh::Result &r, PtBvh *out) {
     static_assert(sizeof(ptbvh::Node) == sizeof(PtBvhNode), "node layouts must match");
     const ptbvh::Node *dn = nullptr;
@@ -228,6 +246,9 @@ static uint32_t scene_features(const PtDeviceScene &D, const pt_scene *s) {
 static void launch_render(uint32_t features, unsigned blocks, cudaStream_t st, const PtDeviceScene &S, const PtRenderArgs &A) {
     // first variant (listed from specialised to general) whose mask covers the scene's features
 #define X(M) if ((features & ~(uint32_t)(M)) == 0) { k_render<(M)><<<blocks, PT_RENDER_THREADS, 0, st>>>(S, A); return; }
+    if (A.coop_max > 0) {          // experiment (PT_COOP_MAX): a family with the warp-cooperative sparse walk, if one covers the scene
+        PT_RENDER_COOP_VARIANTS(X)
+    }
     PT_RENDER_VARIANTS(X)
 #undef X
 }
@@ -308,6 +329,7 @@ extern "C" int pt_upload_scene(pt_context *ctx, const pt_scene *s) {
         std::vector<uint32_t> ids(r.order.size());
         for (size_t i = 0; i < r.order.size(); i++) { ordered[i] = bvh_sph_src[r.order[i]]; ids[i] = bvh_src_ids[r.order[i]]; }
         if ((rc = upload(ctx, ordered, &D.bvh_spheres)) || (rc = upload(ctx, ids, &D.bvh_sphere_ids)) || (rc = upload_bvh(ctx, r, &D.sphere_bvh))) return rc;
+        if ((rc = upload_clusters(ctx, r, &D.sph_clusters, &D.n_sph_clusters))) return rc;
         ctx->bvh_nodes += D.sphere_bvh.n_nodes; ctx->bvh_prims += D.sphere_bvh.n_prims;
     }
 
@@ -352,6 +374,7 @@ extern "C" int pt_upload_scene(pt_context *ctx, const pt_scene *s) {
         if ((rc = upload(ctx, ordered, &D.tris)) || (rc = upload(ctx, r.order, &D.tri_ids)) || (rc = upload(ctx, normals, &D.tri_normals)) ||
             (rc = upload_bvh(ctx, r, &D.tri_bvh)))
             return rc;
+        if ((rc = upload_clusters(ctx, r, &D.tri_clusters, &D.n_tri_clusters))) return rc;
         ctx->bvh_nodes += D.tri_bvh.n_nodes; ctx->bvh_prims += D.tri_bvh.n_prims;
     }
 
@@ -473,6 +496,10 @@ extern "C" int pt_render(pt_context *ctx, const pt_render_params *p) {
             A.log2_sample_lanes = lS;
             // parked lanes before the BRDF code runs (variants with PT_F_DEFER): measured best 32 with textures, else 20
             A.shade_batch = ctx->shade_batch > 0 ? (uint32_t)ctx->shade_batch : ((ctx->features & PT_F_TEX) ? 32u : 20u);
+            // cooperative sparse walks only where exactly one tree exists and it has a cluster cut
+            const bool one_tree = (ctx->scene.tri_bvh.n_nodes != 0) != (ctx->scene.sphere_bvh.n_nodes != 0);
+            const bool has_cut = ctx->scene.tri_bvh.n_nodes ? ctx->scene.n_tri_clusters != 0 : ctx->scene.n_sph_clusters != 0;
+            A.coop_max = (one_tree && has_cut) ? (uint32_t)ctx->coop_max : 0u;
             uint32_t warps_per_tile = 1024u >> (5u - lS);                  // pixels per tile / pixels per warp
             uint64_t warps = (uint64_t)A.n_my_tiles * warps_per_tile;
             const uint32_t wpb = PT_RENDER_THREADS / 32;

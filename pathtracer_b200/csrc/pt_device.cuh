@@ -85,6 +85,12 @@ struct PtDeviceScene {
     uint32_t flags;                 // PT_SCENE_*
     float4 light;                   // spheres[0] (c.xyz, r): the importance-sampled light (main.cpp:683)
     pt_camera cam;
+
+    // cuts of the two BVHs into <= 32 clusters for the warp-cooperative closest hit (pt_cluster.h; PT_F_COOP
+    // variants only; NULL when the tree has no such cut).  [l] = (min.xyz, first | count << 24), [32 + l] = (max.xyz, 0).
+    // Kept at the end: the other members' parameter offsets -- and the SASS of the default variants -- do not move.
+    const float4 *tri_clusters, *sph_clusters;
+    uint32_t n_tri_clusters, n_sph_clusters;
 };
 
 struct PtHit {
@@ -165,5 +171,6 @@ enum : uint32_t {
     PT_F_ALL = 63u | 128u,
     PT_F_DEFER = 64u,     // kernel policy, not a scene feature: park lanes that need a BRDF sample (pt_kernels.cuh)
     PT_F_QUEUE = 256u,    // kernel policy: BVH walks of a CTA are compacted through a shared-memory ray queue (pt_kernels.cuh)
+    PT_F_COOP = 512u,     // kernel policy: sparse BVH walks (few lanes of the warp) are traced one ray at a time by all 32 lanes
     PT_F_LENS = 128u      // thin-lens camera (-d, always in world 4); pinhole-only variants drop that code
 };

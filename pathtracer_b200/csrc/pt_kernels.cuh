@@ -36,6 +36,11 @@ __host__ __device__ constexpr int pt_render_min_blocks(uint32_t F) {
     X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_QUEUE_X) /* the same families with -d */ X(PT_F_TEX | PT_F_LIGHT | PT_F_DEFER | PT_F_LENS) \
     X(PT_F_SPH_BVH | PT_F_LIGHT | PT_F_LENS | PT_F_DEFER) X(PT_F_QUADS | PT_F_LIGHT | PT_F_LENS | PT_F_DEFER_X) X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_LENS) \
     X(PT_F_ALL | PT_F_DEFER)
+// megakernel only: the same families with PT_F_COOP (sparse walks traced warp-cooperatively); launched only when
+// pt_render asks for it (PT_COOP_MAX > 0 and the scene's tree has a cluster cut)
+#define PT_RENDER_COOP_VARIANTS(X) \
+    X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_COOP) X(PT_F_SPH_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_COOP) \
+    X(PT_F_SPH_BVH | PT_F_LENS | PT_F_DEFER_X | PT_F_COOP) X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_LENS | PT_F_COOP)
 
 #define PT_N_COUNTERS 72            // [0] rays [1] NaN retries [2] samples [3] -, then the PT_STATS_HIST experiment's histograms
 
@@ -51,6 +56,7 @@ struct PtRenderArgs {
     uint64_t seed;
     float4 *accum;                      // width*height: sum r,g,b + number of samples
     unsigned long long *counters;       // [0] rays, [1] NaN retries, [2] samples
+    uint32_t coop_max;                  // PT_F_COOP variants: walks entered by <= coop_max lanes are traced cooperatively (last: keeps offsets)
 };
 
 // ---- camera (RenderTexel's two sampling loops, src/win32_main.cpp:1032-1170) ----------------------
@@ -162,6 +168,7 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
     // written to the queue at ballot/atomic-compacted slots, and after a barrier thread k walks ray k -- full warps
     // however sparsely the rays were spread over the CTA's lanes -- and leaves (t, id) in the slot for the owner.
     constexpr bool kQueue = (F & PT_F_QUEUE) && (((F & PT_F_SPH_BVH) != 0) != ((F & PT_F_TRI_BVH) != 0));
+    constexpr bool kCoop = !kQueue && (F & PT_F_COOP) && (((F & PT_F_SPH_BVH) != 0) != ((F & PT_F_TRI_BVH) != 0));
     __shared__ float4 q_o[kQueue ? PT_RENDER_THREADS : 1], q_d[kQueue ? PT_RENDER_THREADS : 1];
     __shared__ uint32_t q_n[2];
     uint32_t q_iter = 0;
@@ -223,13 +230,48 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
             q_iter++;
         }
 
+        // PT_F_COOP: every new ray does the linear lists and the root step itself; then the warp votes.  When few lanes
+        // enter the tree (bounce rays that cross the mesh's box while their neighbours see sky or ground -- 2/3 of the
+        // traversal's warp instructions, profiles/r01e_bvh_walk_occupancy_w5.txt) their rays are traced one after the
+        // other by all 32 lanes over the cluster cut (pt_coop_trace); otherwise each lane walks its own ray as before.
+        if (kCoop) {
+            constexpr int LEAF = (F & PT_F_TRI_BVH) ? PT_LEAF_TRIS : PT_LEAF_SPHERES;
+            const PtBvh &bvh = (F & PT_F_TRI_BVH) ? S.tri_bvh : S.sphere_bvh;
+            int node0 = PT_STACK_SENTINEL, far0 = PT_STACK_SENTINEL;
+            PtRayInv rinv;
+            if (state == NEW_RAY) {
+                h.t = 3.402823466e+38f;
+                h.id = PT_ID_MISS;
+                pt_hit_analytic<F>(S, o, d, pt_dot_exact(d), h);
+                rinv = pt_ray_inv(o, d);
+                pt_bvh_root_step(bvh, rinv, h.t, node0, far0);
+            }
+            __syncwarp();
+            uint32_t m = __ballot_sync(0xffffffffu, node0 != PT_STACK_SENTINEL);
+            if (m != 0u) {
+                if ((uint32_t)__popc(m) <= A.coop_max) {
+                    const float4 *cl = (F & PT_F_TRI_BVH) ? S.tri_clusters : S.sph_clusters;
+                    const uint32_t ncl = (F & PT_F_TRI_BVH) ? S.n_tri_clusters : S.n_sph_clusters;
+#pragma unroll 1
+                    while (m != 0u) {
+                        const int src = __ffs((int)m) - 1;
+                        m &= m - 1u;
+                        pt_coop_trace<LEAF>(S, cl, ncl, src, lane, o, d, h);
+                    }
+                } else if (node0 != PT_STACK_SENTINEL) {
+                    pt_bvh_walk_from<LEAF>(S, bvh, rinv, o, d, pt_dot_exact(d), h, node0, far0);
+                }
+            }
+            __syncwarp();
+        }
+
         // ---- closest hit, emission, termination rules of RayCast (main.cpp:579-590, 799) ----
         bool done = false;
         if (state == NEW_RAY) {
 #ifdef PT_STATS_HIST
             g_pt_hist = A.counters;
 #endif
-            if (!kQueue) h = pt_closest_hit<F>(S, o, d);
+            if (!kQueue && !kCoop) h = pt_closest_hit<F>(S, o, d);
             n_rays++;
             float3 n;
             uint32_t mat;

@@ -227,6 +227,117 @@ struct PtWalker {
     }
 };
 
+// ---- sparse walks: the root step on its own, and the walk resumed below it ---------------------------
+// (PT_F_COOP variants only.)  The kernel first asks every new ray whether it enters the tree at all; the warp then
+// votes on HOW the entering rays are traced, so the root step is split off the walk and its outcome handed on:
+// `node` = the child to descend first (PT_STACK_SENTINEL: the ray misses both), `far` = the other child when both are hit.
+__device__ __forceinline__ void pt_bvh_root_step(const PtBvh &bvh, const PtRayInv &r, float tmax, int &node, int &far) {
+    const float4 *nodes = reinterpret_cast<const float4 *>(bvh.nodes);
+    const int4 link = __ldg(reinterpret_cast<const int4 *>(nodes + 3));
+    bool hl, hr;
+    float ln, rn;
+    pt_node_slabs(__ldg(nodes), __ldg(nodes + 1), __ldg(nodes + 2), r, tmax, hl, hr, ln, rn);
+    node = far = PT_STACK_SENTINEL;
+    if (hl && hr) {
+        const bool left_first = ln <= rn;
+        node = left_first ? link.x : link.y;
+        far = left_first ? link.y : link.x;
+    } else if (hl) node = link.x;
+    else if (hr) node = link.y;
+}
+
+template <int LEAF>
+__device__ __forceinline__ void pt_bvh_walk_from(const PtDeviceScene &S, const PtBvh &bvh, const PtRayInv &r, float3 o, float3 d, float a,
+                                                 PtHit &h, int node, int far) {
+    int stack[PT_STACK_DEPTH];
+    stack[0] = PT_STACK_SENTINEL;
+    int sp = 1;
+    if (far != PT_STACK_SENTINEL) stack[sp++] = far;
+    const float4 *nodes = reinterpret_cast<const float4 *>(bvh.nodes);
+    while (node != PT_STACK_SENTINEL) {
+        while (node >= 0) {
+            const float4 b0 = __ldg(nodes + 4 * node), b1 = __ldg(nodes + 4 * node + 1), b2 = __ldg(nodes + 4 * node + 2);
+            const int4 link = __ldg(reinterpret_cast<const int4 *>(nodes + 4 * node + 3));
+            bool hl, hr;
+            float ln, rn;
+            pt_node_slabs(b0, b1, b2, r, h.t, hl, hr, ln, rn);
+            if (hl && hr) {
+                bool left_first = ln <= rn;
+                stack[sp++] = left_first ? link.y : link.x;
+                node = left_first ? link.x : link.y;
+            } else if (hl) node = link.x;
+            else if (hr) node = link.y;
+            else node = stack[--sp];
+        }
+        if (node != PT_STACK_SENTINEL) {
+            pt_leaf_test<LEAF>(S, node, o, d, a, h);
+            node = stack[--sp];
+        }
+    }
+}
+
+// ---- warp-cooperative closest hit of ONE ray (the ray of lane `src`), executed by all 32 lanes ----------
+// `cl` is the cut of the tree into n <= 32 clusters (pt_cluster.h).  Lane l tests cluster l's box; the clusters the
+// ray enters are then taken nearest first (REDUX.MIN over the entry distances) until the next one lies behind the
+// best hit; the lanes test a cluster's primitives 32 at a time with the same per-primitive functions as the walk,
+// and two REDUX.MINs take the lexicographic minimum of (t, id) -- t > 0, so its bit pattern orders like the float.
+// pt_accept keeps exactly that minimum over the same candidates, so the hit is bit-identical to the walk's.
+// Must be called by the whole, converged warp.  ~100 warp instructions for a ray that crosses the mesh's box and
+// misses; a BVH2 walk costs the warp 15-30 node steps of ~55 instructions however few lanes take part.
+template <int LEAF>
+__device__ __forceinline__ void pt_coop_trace(const PtDeviceScene &S, const float4 *__restrict__ cl, uint32_t n_clusters, int src,
+                                              uint32_t lane, float3 o, float3 d, PtHit &h) {
+    const uint32_t FULL = 0xffffffffu;
+    const float3 O = f3(__shfl_sync(FULL, o.x, src), __shfl_sync(FULL, o.y, src), __shfl_sync(FULL, o.z, src));
+    const float3 D = f3(__shfl_sync(FULL, d.x, src), __shfl_sync(FULL, d.y, src), __shfl_sync(FULL, d.z, src));
+    float bt = __shfl_sync(FULL, h.t, src);
+    uint32_t bid = __shfl_sync(FULL, h.id, src);
+    const PtRayInv r = pt_ray_inv(O, D);
+    const float a = (LEAF == PT_LEAF_SPHERES) ? pt_dot_exact(D) : 0.f;
+    const float4 mn = __ldg(cl + lane), mx = __ldg(cl + 32 + lane);
+    const float x0 = fmaf(mn.x, r.inv.x, -r.ood.x), x1 = fmaf(mx.x, r.inv.x, -r.ood.x);
+    const float y0 = fmaf(mn.y, r.inv.y, -r.ood.y), y1 = fmaf(mx.y, r.inv.y, -r.ood.y);
+    const float z0 = fmaf(mn.z, r.inv.z, -r.ood.z), z1 = fmaf(mx.z, r.inv.z, -r.ood.z);
+    const float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), 0.f));
+    const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), bt)) * 1.0000004f;
+    bool pend = lane < n_clusters && tn <= tf;
+    const uint32_t tnb = __float_as_uint(tn);                  // tn >= 0: ordered like the float
+#pragma unroll 1
+    while (true) {
+        const uint32_t nb = __reduce_min_sync(FULL, pend ? tnb : 0xFFFFFFFFu);
+        if (nb == 0xFFFFFFFFu || __uint_as_float(nb) > bt * 1.0000004f) break;     // none left, or all behind the best hit
+        const int c = __ffs((int)__ballot_sync(FULL, pend && tnb == nb)) - 1;
+        if ((int)lane == c) pend = false;
+        const uint32_t fc = __shfl_sync(FULL, __float_as_uint(mn.w), c);           // first | count << 24
+        const uint32_t first = fc & 0xFFFFFFu, count = fc >> 24;
+#pragma unroll 1
+        for (uint32_t base = 0; base < count; base += 32u) {
+            const uint32_t pos = first + base + lane;
+            float t = -1.f;
+            if (base + lane < count) {
+                if (LEAF == PT_LEAF_TRIS) {
+                    const float4 *rec = reinterpret_cast<const float4 *>(S.tris + pos);
+                    t = pt_planar_t<false>(O, D, __ldg(rec), __ldg(rec + 1), __ldg(rec + 2), PT_MIN_HIT);
+                } else {
+                    t = pt_sphere_t(O, D, a, __ldg(S.bvh_spheres + pos));
+                }
+            }
+            const bool ok = t > 0.f && t <= bt;
+            if (__any_sync(FULL, ok)) {
+                const uint32_t tb = ok ? __float_as_uint(t) : 0x7f7fffffu;
+                const uint32_t tmin = __reduce_min_sync(FULL, tb);
+                uint32_t ii = PT_ID_MISS;
+                if (ok && tb == tmin)
+                    ii = (LEAF == PT_LEAF_TRIS) ? PT_ID(PT_HIT_TRIANGLE, __ldg(S.tri_ids + pos)) : PT_ID(PT_HIT_SPHERE, __ldg(S.bvh_sphere_ids + pos));
+                const uint32_t imin = __reduce_min_sync(FULL, ii);
+                const float tt = __uint_as_float(tmin);
+                if (tt < bt || (tt == bt && imin < bid)) { bt = tt; bid = imin; }
+            }
+        }
+    }
+    if ((int)lane == src) { h.t = bt; h.id = bid; }
+}
+
 // the analytic (linear-list) part of the closest hit: spheres, quads, planes, boxes
 template <uint32_t F>
 __device__ __forceinline__ void pt_hit_analytic(const PtDeviceScene &S, float3 o, float3 d, float a, PtHit &h) {
