@@ -51,7 +51,10 @@ struct pt_context {
     bool sah_sweep = true;                     // PT_SAH_SWEEP=0: 16-bin SAH everywhere (experiment)
     int tri_leaf = 4, sph_leaf = 2;            // max primitives per BVH leaf (PT_TRI_LEAF / PT_SPH_LEAF; measured, profiles/r01f)
     int shade_batch = 0;                       // PT_SHADE_BATCH: deferral threshold of k_render (0 = per-variant default)
-    int coop_max = 0;                          // PT_COOP_MAX: walks entered by <= this many lanes of a warp are traced cooperatively (0 = off)
+    // Walks entered by <= coop_max lanes of a warp are traced cooperatively (k_render<... | PT_F_COOP>).  -1 = the measured
+    // default: 12 for a triangle tree (w5 +8.4 %), off for a sphere tree (w2 -0.5 %, w4 +0.6 %; profiles/r01h_coop_check.jsonl).
+    // PT_COOP_MAX=n overrides it for both kinds of tree (0 = off).
+    int coop_max = -1;
     // single-process multi-GPU (pt_gather_tiles_from / pt_add_accum_from)
     void *pack_buf = nullptr, *stage_buf = nullptr;
     size_t pack_bytes = 0, stage_bytes = 0;
@@ -202,9 +205,13 @@ static PtPlanar make_planar(const float *A, const float *u, const float *v) {
 }
 
 // the <= 32-cluster cut of a tree for the PT_F_COOP variants; *out stays NULL when the tree has no such cut
-static int upload_clusters(pt_context *ctx, const ptbvh::Result &r, const float4 **out, uint32_t *n_out) {
+static int coop_threshold(const pt_context *ctx, bool triangles) {
+    return ctx->coop_max >= 0 ? ctx->coop_max : (triangles ? 12 : 0);
+}
+
+static int upload_clusters(pt_context *ctx, const ptbvh::Result &r, bool triangles, const float4 **out, uint32_t *n_out) {
     *out = nullptr; *n_out = 0;
-    if (ctx->coop_max <= 0) return PT_OK;
+    if (coop_threshold(ctx, triangles) <= 0) return PT_OK;
     const ptbvh::ClusterCut cut = ptbvh::build_cut(r);
     if (cut.clusters.empty()) return PT_OK;
     const std::vector<float> img = cut.image();
@@ -246,7 +253,7 @@ static uint32_t scene_features(const PtDeviceScene &D, const pt_scene *s) {
 static void launch_render(uint32_t features, unsigned blocks, cudaStream_t st, const PtDeviceScene &S, const PtRenderArgs &A) {
     // first variant (listed from specialised to general) whose mask covers the scene's features
 #define X(M) if ((features & ~(uint32_t)(M)) == 0) { k_render<(M)><<<blocks, PT_RENDER_THREADS, 0, st>>>(S, A); return; }
-    if (A.coop_max > 0) {          // experiment (PT_COOP_MAX): a family with the warp-cooperative sparse walk, if one covers the scene
+    if (A.coop_max > 0) {          // a family with the warp-cooperative sparse walk, if one covers the scene
         PT_RENDER_COOP_VARIANTS(X)
     }
     PT_RENDER_VARIANTS(X)
@@ -329,7 +336,7 @@ extern "C" int pt_upload_scene(pt_context *ctx, const pt_scene *s) {
         std::vector<uint32_t> ids(r.order.size());
         for (size_t i = 0; i < r.order.size(); i++) { ordered[i] = bvh_sph_src[r.order[i]]; ids[i] = bvh_src_ids[r.order[i]]; }
         if ((rc = upload(ctx, ordered, &D.bvh_spheres)) || (rc = upload(ctx, ids, &D.bvh_sphere_ids)) || (rc = upload_bvh(ctx, r, &D.sphere_bvh))) return rc;
-        if ((rc = upload_clusters(ctx, r, &D.sph_clusters, &D.n_sph_clusters))) return rc;
+        if ((rc = upload_clusters(ctx, r, false, &D.sph_clusters, &D.n_sph_clusters))) return rc;
         ctx->bvh_nodes += D.sphere_bvh.n_nodes; ctx->bvh_prims += D.sphere_bvh.n_prims;
     }
 
@@ -374,7 +381,7 @@ extern "C" int pt_upload_scene(pt_context *ctx, const pt_scene *s) {
         if ((rc = upload(ctx, ordered, &D.tris)) || (rc = upload(ctx, r.order, &D.tri_ids)) || (rc = upload(ctx, normals, &D.tri_normals)) ||
             (rc = upload_bvh(ctx, r, &D.tri_bvh)))
             return rc;
-        if ((rc = upload_clusters(ctx, r, &D.tri_clusters, &D.n_tri_clusters))) return rc;
+        if ((rc = upload_clusters(ctx, r, true, &D.tri_clusters, &D.n_tri_clusters))) return rc;
         ctx->bvh_nodes += D.tri_bvh.n_nodes; ctx->bvh_prims += D.tri_bvh.n_prims;
     }
 
@@ -499,7 +506,7 @@ extern "C" int pt_render(pt_context *ctx, const pt_render_params *p) {
             // cooperative sparse walks only where exactly one tree exists and it has a cluster cut
             const bool one_tree = (ctx->scene.tri_bvh.n_nodes != 0) != (ctx->scene.sphere_bvh.n_nodes != 0);
             const bool has_cut = ctx->scene.tri_bvh.n_nodes ? ctx->scene.n_tri_clusters != 0 : ctx->scene.n_sph_clusters != 0;
-            A.coop_max = (one_tree && has_cut) ? (uint32_t)ctx->coop_max : 0u;
+            A.coop_max = (one_tree && has_cut) ? (uint32_t)coop_threshold(ctx, ctx->scene.tri_bvh.n_nodes != 0) : 0u;
             uint32_t warps_per_tile = 1024u >> (5u - lS);                  // pixels per tile / pixels per warp
             uint64_t warps = (uint64_t)A.n_my_tiles * warps_per_tile;
             const uint32_t wpb = PT_RENDER_THREADS / 32;

@@ -36,8 +36,8 @@ __host__ __device__ constexpr int pt_render_min_blocks(uint32_t F) {
     X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_QUEUE_X) /* the same families with -d */ X(PT_F_TEX | PT_F_LIGHT | PT_F_DEFER | PT_F_LENS) \
     X(PT_F_SPH_BVH | PT_F_LIGHT | PT_F_LENS | PT_F_DEFER) X(PT_F_QUADS | PT_F_LIGHT | PT_F_LENS | PT_F_DEFER_X) X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_LENS) \
     X(PT_F_ALL | PT_F_DEFER)
-// megakernel only: the same families with PT_F_COOP (sparse walks traced warp-cooperatively); launched only when
-// pt_render asks for it (PT_COOP_MAX > 0 and the scene's tree has a cluster cut)
+// megakernel only: the same families with PT_F_COOP (sparse walks traced warp-cooperatively); launched when the scene's
+// one tree has a cluster cut and the threshold is > 0 (default: triangle trees, 12 lanes; PT_COOP_MAX overrides)
 #define PT_RENDER_COOP_VARIANTS(X) \
     X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_COOP) X(PT_F_SPH_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_COOP) \
     X(PT_F_SPH_BVH | PT_F_LENS | PT_F_DEFER_X | PT_F_COOP) X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_LENS | PT_F_COOP)

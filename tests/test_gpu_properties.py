@@ -128,6 +128,31 @@ def test_wavefront_kernel_renders_the_same_samples(worlds, w, lens):
     assert (b0 == b1).mean() > 0.999
 
 
+@pytest.mark.parametrize("w,lens", [(5, False), (5, True), (2, False), (4, False)])
+def test_cooperative_sparse_walks_do_not_change_the_samples(worlds, w, lens, monkeypatch):
+    """The PT_F_COOP kernel family traces the walks that few lanes of a warp enter one ray at a time with all 32
+    lanes over the cluster cut of the tree (pt_cluster.h, pt_coop_trace): the same candidates, the same
+    (t, id) minimum -- bit-identical sums and ray counts for any threshold, on triangle and sphere trees.
+    (CPU side of the argument: tests/test_clusters.py.)"""
+    W, H, pp = 200, 120, 5
+    sc = worlds(w).scene(W, H, lens=lens)
+    res = []
+    for coop in ("0", None, "1", "5", "32"):            # off, the default (12 for triangles, off for spheres), thresholds
+        if coop is None:
+            monkeypatch.delenv("PT_COOP_MAX", raising=False)
+        else:
+            monkeypatch.setenv("PT_COOP_MAX", coop)
+        rc = render.RenderCore(0)                        # the environment is read by pt_create
+        rc.upload_scene(sc)
+        rc.render(W, H, pp, seed=11)
+        _, a, st = rc.readback(False, True)
+        res.append((a.copy(), st.rays, st.nan_retries))
+        rc.close()
+    for a, rays, nan in res[1:]:
+        assert np.array_equal(a.view(np.uint32), res[0][0].view(np.uint32))
+        assert rays == res[0][1] and nan == res[0][2]
+
+
 @pytest.mark.parametrize("batch", [1, 8, 32])
 def test_shade_deferral_does_not_change_the_samples(worlds, batch, monkeypatch):
     """Parking lanes until `shade_batch` of them need a BRDF sample is scheduling only: bit-identical sums."""
