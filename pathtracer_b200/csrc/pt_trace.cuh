@@ -76,6 +76,12 @@ __device__ __forceinline__ void pt_accept(PtHit &h, float t, uint32_t id) {
 enum { PT_LEAF_SPHERES = 0, PT_LEAF_TRIS = 1 };
 #define PT_STACK_SENTINEL ((int)0x80000000)
 
+__device__ __forceinline__ float pt_rcp_approx(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
 struct PtRayInv {          // per-ray constants of the slab test
     float3 inv, ood;
 };
@@ -85,8 +91,9 @@ __device__ __forceinline__ PtRayInv pt_ray_inv(float3 o, float3 d) {
                    fabsf(d.y) < 1e-20f ? copysignf(1e-20f, d.y) : d.y,
                    fabsf(d.z) < 1e-20f ? copysignf(1e-20f, d.z) : d.z);
     PtRayInv r;
-    // MUFU.RCP (<= 1 ulp): the slab test below is conservative by 4e-7 relative and the boxes are padded
-    r.inv = f3(__fdividef(1.0f, dd.x), __fdividef(1.0f, dd.y), __fdividef(1.0f, dd.z));
+    // one MUFU.RCP each (<= 1 ulp): the slab test below is conservative by 4e-7 relative and the boxes are padded.
+    // (__fdividef(1.0f, x) returns the same value for 1e-20 <= |x| <= 1 but wraps the MUFU in range handling: 8 instructions.)
+    r.inv = f3(pt_rcp_approx(dd.x), pt_rcp_approx(dd.y), pt_rcp_approx(dd.z));
     r.ood = f3(o.x * r.inv.x, o.y * r.inv.y, o.z * r.inv.z);
     return r;
 }

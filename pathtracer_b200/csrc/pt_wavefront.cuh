@@ -132,7 +132,7 @@ k_render_wf(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtR
                 }
                 if (s < A.s_end) {
                     PtRng rng;
-                    pt_camera_ray<F>(S.cam, A.width, A.height, A.pp, A.pp_magic, WF_PIXEL_X(p), WF_PIXEL_Y(p), s, retry, A.seed, rng, o, d);
+                    pt_camera_ray<F>(S.cam, pt_pixel_cam(A.width, A.height, A.pp, WF_PIXEL_X(p), WF_PIXEL_Y(p)), A.pp, A.pp_magic, s, retry, A.seed, rng, o, d);
                     wf_st3(W, WF_BX, p, f3(1, 1, 1));
                     wf_st3(W, WF_LX, p, f3(0, 0, 0));
                     misc = (retry << 8) | (rng.blk << 16);                   // depth 0
