@@ -194,7 +194,9 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
 
     while (true) {
         if (state == NO_RAY && s < A.s_end) {
-            pt_camera_ray<F>(S.cam, pxc, A.pp, A.pp_magic, s, retry, A.seed, rng, o, d);
+            // thin-lens variants keep the per-sample evaluation: holding fx, fy across the loop cost w4 1.5 % (profiles/r01h_ab_*)
+            if (F & PT_F_LENS) pt_camera_ray<F>(S.cam, pt_pixel_cam(A.width, A.height, A.pp, x, y), A.pp, A.pp_magic, s, retry, A.seed, rng, o, d);
+            else pt_camera_ray<F>(S.cam, pxc, A.pp, A.pp_magic, s, retry, A.seed, rng, o, d);
             beta = f3(1, 1, 1);
             L = f3(0, 0, 0);
             depth = 0;

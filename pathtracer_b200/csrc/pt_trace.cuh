@@ -85,6 +85,7 @@ __device__ __forceinline__ float pt_rcp_approx(float x) {
 struct PtRayInv {          // per-ray constants of the slab test
     float3 inv, ood;
 };
+template <bool BARE_RCP = true>
 __device__ __forceinline__ PtRayInv pt_ray_inv(float3 o, float3 d) {
     // reciprocal direction with zero components nudged so that no inf*0 appears in the slab test
     float3 dd = f3(fabsf(d.x) < 1e-20f ? copysignf(1e-20f, d.x) : d.x,
@@ -93,7 +94,10 @@ __device__ __forceinline__ PtRayInv pt_ray_inv(float3 o, float3 d) {
     PtRayInv r;
     // one MUFU.RCP each (<= 1 ulp): the slab test below is conservative by 4e-7 relative and the boxes are padded.
     // (__fdividef(1.0f, x) returns the same value for 1e-20 <= |x| <= 1 but wraps the MUFU in range handling: 8 instructions.)
-    r.inv = f3(pt_rcp_approx(dd.x), pt_rcp_approx(dd.y), pt_rcp_approx(dd.z));
+    // Measured (profiles/r01h_ab_*): the bare form gains everywhere (w5 with the hoisted camera constants +4.4 %, w2 +1.4 %) except
+    // in the thin-lens sphere family (w4 -1.4 %, although the kernel is 16 instructions shorter), which keeps __fdividef.
+    if (BARE_RCP) r.inv = f3(pt_rcp_approx(dd.x), pt_rcp_approx(dd.y), pt_rcp_approx(dd.z));
+    else r.inv = f3(__fdividef(1.0f, dd.x), __fdividef(1.0f, dd.y), __fdividef(1.0f, dd.z));
     r.ood = f3(o.x * r.inv.x, o.y * r.inv.y, o.z * r.inv.z);
     return r;
 }
@@ -147,9 +151,9 @@ __device__ __forceinline__ void pt_leaf_test(const PtDeviceScene &S, int node, f
 #ifdef PT_STATS_HIST
 __device__ unsigned long long *g_pt_hist;     // experiment build only
 #endif
-template <int LEAF>
+template <int LEAF, bool BARE_RCP = true>
 __device__ __forceinline__ void pt_bvh_walk(const PtDeviceScene &S, const PtBvh &bvh, float3 o, float3 d, float a, PtHit &h) {
-    const PtRayInv r = pt_ray_inv(o, d);
+    const PtRayInv r = pt_ray_inv<BARE_RCP>(o, d);
 #ifdef PT_STATS_HIST
     const bool enters = pt_bvh_root_hit(bvh, r, h.t);
     const uint32_t n_enter = __popc(__ballot_sync(__activemask(), enters));
@@ -384,7 +388,7 @@ __device__ __forceinline__ PtHit pt_closest_hit(const PtDeviceScene &S, float3 o
     h.id = PT_ID_MISS;
     const float a = pt_dot_exact(d);
     pt_hit_analytic<F>(S, o, d, a, h);
-    if ((F & PT_F_SPH_BVH) && S.sphere_bvh.n_prims) pt_bvh_walk<PT_LEAF_SPHERES>(S, S.sphere_bvh, o, d, a, h);
+    if ((F & PT_F_SPH_BVH) && S.sphere_bvh.n_prims) pt_bvh_walk<PT_LEAF_SPHERES, !(F & PT_F_LENS)>(S, S.sphere_bvh, o, d, a, h);
     if ((F & PT_F_TRI_BVH) && S.tri_bvh.n_prims) pt_bvh_walk<PT_LEAF_TRIS>(S, S.tri_bvh, o, d, a, h);
     return h;
 }
