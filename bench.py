@@ -110,6 +110,13 @@ class ClockSampler(threading.Thread):
         super().__init__(daemon=True)
         self.index, self.rows, self._stop = index, [], threading.Event()
         self.proc = None
+        self.t_begin = self.t_end = None        # host timestamps of the timed region; rows outside it are dropped
+
+    def mark_begin(self):
+        self.t_begin = time.monotonic()
+
+    def mark_end(self):
+        self.t_end = time.monotonic()
 
     def run(self):
         q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -118,7 +125,7 @@ class ClockSampler(threading.Thread):
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "100"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             for line in self.proc.stdout:
-                self.rows.append([x.strip() for x in line.split(",")])
+                self.rows.append([x.strip() for x in line.split(",")] + [time.monotonic()])
                 if self._stop.is_set():
                     break
         except Exception:
@@ -128,7 +135,12 @@ class ClockSampler(threading.Thread):
         self._stop.set()
         if self.proc:
             self.proc.terminate()
-        rows = [r for r in self.rows if len(r) >= 7 and r[0].isdigit()]
+        rows = [r for r in self.rows if len(r) >= 8 and r[0].isdigit()]
+        if self.t_begin is not None and self.t_end is not None:
+            # nvidia-smi is started before the warm-up (it needs ~0.5 s to come up); keep the samples of the timed region,
+            # one sampling period of slack on the far side
+            inside = [r for r in rows if self.t_begin <= r[-1] <= self.t_end + 0.1]
+            rows = inside or [r for r in rows if r[-1] >= self.t_begin]
         if not rows:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
         sm = sorted(int(r[0]) for r in rows)
@@ -187,16 +199,17 @@ def run_b200(a):
         torch.cuda.synchronize()
 
     # ---- device-resident metric -------------------------------------------------------------
+    sampler = ClockSampler(local)
+    sampler.start()                                     # before the warm-up: it is up and sampling when the timed region starts
     for i in range(a.warmup):
         core.flush_l2()                                 # also allocates the scratch buffer outside the timed region
         frame.render(a.pp, seed=100 + i)
     barrier()
-    sampler = ClockSampler(local)
-    sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     k_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(a.steps)]
     launches = 0
     barrier()
+    sampler.mark_begin()
     e0.record()
     for i in range(a.steps):
         core.flush_l2()                                 # 256 MiB memset > 126 MB L2, between timed iterations (inside the region)
@@ -206,6 +219,7 @@ def run_b200(a):
         launches += frame.launches
     e1.record()
     barrier()
+    sampler.mark_end()
     clocks = sampler.stop()
     ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
     if world > 1:
