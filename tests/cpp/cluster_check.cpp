@@ -182,3 +182,41 @@ extern "C" int cluster_check(const float *boxes, const float *tris, uint32_t n, 
     out->coop_clusters_per_ray = (double)visited / n_rays;
     return 0;
 }
+
+// per-ray work of the BVH2 walk and of the cooperative trace for caller-supplied rays (tools/walk_model.py):
+// node steps, leaf primitive tests, clusters visited, 32-wide primitive rounds
+extern "C" int walk_profile(const float *boxes, const float *tris, uint32_t n, int max_leaf, uint32_t n_rays, const float *o, const float *d,
+                            uint32_t *steps, uint32_t *prim_tests, uint32_t *clusters, uint32_t *rounds, uint32_t *hit) {
+    std::vector<Box> pb(n);
+    for (uint32_t i = 0; i < n; i++) for (int k = 0; k < 3; k++) { pb[i].mn[k] = boxes[6 * i + k]; pb[i].mx[k] = boxes[6 * i + 3 + k]; }
+    Result R = Builder(pb, max_leaf).build();
+    ClusterCut cut = build_cut(R);
+    if (cut.clusters.empty()) return 1;
+    std::vector<float> img = cut.image();
+    for (uint32_t i = 0; i < n_rays; i++) {
+        Ray r = make_ray(o + 3 * i, d + 3 * i);
+        // the walk, counting primitive tests as well
+        Hit h{3.402823466e+38f, 0xFFFFFFFFu};
+        std::vector<int32_t> st{0};
+        uint32_t ns = 0, np = 0;
+        while (!st.empty()) {
+            int32_t node = st.back(); st.pop_back();
+            if (node < 0) {
+                uint32_t enc = (uint32_t)~node, first = enc & 0xFFFFFFu, count = enc >> 24;
+                for (uint32_t k = 0; k < count; k++) { np++; uint32_t id = R.order[first + k]; float t = tri_t(tris + 9 * id, r.o, r.d); if (t > 0.f && t <= h.t) accept(h, t, id); }
+                continue;
+            }
+            ns++;
+            const Node &nd = R.nodes[node];
+            float ln, rn;
+            bool hl = slab(nd.b, nd.b + 3, r, h.t, ln), hr = slab(nd.b + 6, nd.b + 9, r, h.t, rn);
+            if (hl && hr) { bool lf = ln <= rn; st.push_back(lf ? nd.link[1] : nd.link[0]); st.push_back(lf ? nd.link[0] : nd.link[1]); }
+            else if (hl) st.push_back(nd.link[0]);
+            else if (hr) st.push_back(nd.link[1]);
+        }
+        uint64_t rd = 0, vis = 0;
+        coop(img, (uint32_t)cut.clusters.size(), R, tris, r, rd, vis);
+        steps[i] = ns; prim_tests[i] = np; clusters[i] = (uint32_t)vis; rounds[i] = (uint32_t)rd; hit[i] = h.id != 0xFFFFFFFFu;
+    }
+    return 0;
+}
