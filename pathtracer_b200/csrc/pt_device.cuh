@@ -111,8 +111,30 @@ __device__ __forceinline__ float dot3(float4 a, float3 b) { return a.x * b.x + a
 __device__ __forceinline__ float3 cross3(float3 a, float3 b) {
     return f3(a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y);
 }
+// Fast divide and reciprocal square root.  Default: the CUDA intrinsics (a MUFU plus range handling: |y| > 2^126 for the
+// divide, denormal arguments for the rsqrt -- cases this path never produces).  -DPT_X_BARE_MUFU (experiment build,
+// tools/r02_experiments.sh) issues the bare MUFU.RCP / MUFU.RSQ instead: same values on the normal range, ~5 instructions
+// fewer per call; to be adopted only if tools/ab_identity.py shows every output bit-identical.
+__device__ __forceinline__ float pt_fdiv(float x, float y) {
+#ifdef PT_X_BARE_MUFU
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(y));
+    return x * r;
+#else
+    return __fdividef(x, y);
+#endif
+}
+__device__ __forceinline__ float pt_rsqrt(float x) {
+#ifdef PT_X_BARE_MUFU
+    float r;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+#else
+    return rsqrtf(x);
+#endif
+}
 __device__ __forceinline__ float3 normalize3(float3 a) {
-    float inv = rsqrtf(dot3(a, a));
+    float inv = pt_rsqrt(dot3(a, a));
     return inv * a;
 }
 __device__ __forceinline__ bool isnan3(float3 a) { return (a.x != a.x) || (a.y != a.y) || (a.z != a.z); }

@@ -114,7 +114,7 @@ __device__ __forceinline__ void pt_camera_ray(const pt_camera &c, const PtPixelC
         const float fpd = 1.f / (1.f / 0.098f - 1.f / c.focal_length);       // == focal_distance
         const float3 N = -f3(c.axis_z);
         const float3 pp0 = pos + ax + fpd * N;
-        float t = __fdividef(dot3(N, pp0) - dot3(N, pos), dot3(N, dir));
+        float t = pt_fdiv(dot3(N, pp0) - dot3(N, pos), dot3(N, dir));
         float3 focal = pos + t * dir;
         float2 ds = c_poisson_disk[(r2 * ri) % 12u];
         o = pos + (ds.x * c.aperture_radius) * ax + (ds.y * c.aperture_radius) * ay;

@@ -60,8 +60,8 @@ __device__ __forceinline__ float pt_pdf_to_sphere(float3 dir, float4 light, floa
     float t = pt_sphere_t(from, dir, pt_dot_exact(dir), light);
     if (!(t > 0.f)) return 0.f;
     float3 rel = f3(from.x - light.x, from.y - light.y, from.z - light.z);
-    float cmax = sqrtf(1.f - __fdividef(light.w * light.w, dot3(rel, rel)));
-    return __fdividef(1.f, 2.f * PT_PI * (1.f - cmax));
+    float cmax = sqrtf(1.f - pt_fdiv(light.w * light.w, dot3(rel, rel)));
+    return pt_fdiv(1.f, 2.f * PT_PI * (1.f - cmax));
 }
 
 struct PtSurface {            // what RayCast reads from material_t for a non-emissive hit
@@ -98,7 +98,7 @@ __device__ __forceinline__ bool pt_shade_vertex(const PtDeviceScene &S, PtRng &r
 
     float cos_theta = dot3(n, d);
     cos_theta = (cos_theta > 0.f) ? -cos_theta : cos_theta;                 // main.cpp:596-598
-    float f = __fdividef(1.003f - m.ior, 1.003f + m.ior);
+    float f = pt_fdiv(1.003f - m.ior, 1.003f + m.ior);
     const float F0 = f * f;                                                  // main.cpp:600
     const float3 P = f3(fmaf(t, d.x, o.x), fmaf(t, d.y, o.y), fmaf(t, d.z, o.z));
     const float3 V = -d;
@@ -146,7 +146,7 @@ __device__ __forceinline__ bool pt_shade_vertex(const PtDeviceScene &S, PtRng &r
             } else {
                 // RandomToSphere, main.cpp:2332-2353; the basis is re-aimed at the light and STAYS so
                 float3 dirl = f3(light.x - P.x, light.y - P.y, light.z - P.z);
-                float term1 = 1.f - __fdividef(light.w * light.w, dot3(dirl, dirl));
+                float term1 = 1.f - pt_fdiv(light.w * light.w, dot3(dirl, dirl));
                 if (term1 < 0.f) {
                     r = f3(0, 0, 0);
                 } else {
@@ -161,7 +161,7 @@ __device__ __forceinline__ bool pt_shade_vertex(const PtDeviceScene &S, PtRng &r
                               r.x * tx.z + r.y * ty.z + r.z * tz.z));
             H = normalize3(L + V);
             // cosine pdf of the LOCAL sample (for light samples: measured from the cone axis, main.cpp:709)
-            float pc = fmaxf(0.f, r.z * rsqrtf(dot3(r, r)) * (1.0f / PT_PI));
+            float pc = fmaxf(0.f, r.z * pt_rsqrt(dot3(r, r)) * (1.0f / PT_PI));
             if (use_light) px = 0.5f * pc + 0.5f * pt_pdf_to_sphere(L, light, P);
             else px = pc;
             if (px == 0.f) continue;                                         // main.cpp:722
@@ -169,7 +169,7 @@ __device__ __forceinline__ bool pt_shade_vertex(const PtDeviceScene &S, PtRng &r
             // RandomHalfVectorGGX, main.cpp:2271-2285: cos(theta) = sqrt((1-z2)/(1+z2(a2-1)))
             float a2 = roughness * roughness * roughness * roughness;
             float z2 = u32_to_unit(u.z);
-            float ct = sqrtf(__fdividef(1.f - z2, 1.f + z2 * (a2 - 1.f)));
+            float ct = sqrtf(pt_fdiv(1.f - z2, 1.f + z2 * (a2 - 1.f)));
             float st = sqrtf(fmaxf(0.f, 1.f - ct * ct));
             float sn, cs;
             sincospif(2.f * u32_to_unit(u.y), &sn, &cs);
@@ -200,8 +200,8 @@ __device__ __forceinline__ bool pt_shade_vertex(const PtDeviceScene &S, PtRng &r
         // ks * Hammon G * |H.L| / (|N.L| |H.N|), main.cpp:1610-1620, 1773-1781
         float a2 = roughness * roughness * roughness * roughness;
         float denom = NdotV * sqrtf(a2 + (1.f - a2) * NdotL * NdotL) + NdotL * sqrtf(a2 + (1.f - a2) * NdotV * NdotV);
-        float G = __fdividef(2.f * NdotL * NdotV, denom);
-        float wgt = G * __fdividef(fabsf(dot3(H, L)), fabsf(NdotL) * fabsf(dot3(H, N)));
+        float G = pt_fdiv(2.f * NdotL * NdotV, denom);
+        float wgt = G * pt_fdiv(fabsf(dot3(H, L)), fabsf(NdotL) * fabsf(dot3(H, N)));
         brdf = wgt * ks;
     } else {
         // N.L * kd * albedo / pi with kd = (1 - ks)(1 - metalness), main.cpp:751-759, 772, 1595-1608
@@ -210,7 +210,7 @@ __device__ __forceinline__ bool pt_shade_vertex(const PtDeviceScene &S, PtRng &r
         float q = (1.f - metalness) * NdotL * (1.0f / PT_PI);
         brdf = f3(q * (1.f - ks.x) * albedo.x, q * (1.f - ks.y) * albedo.y, q * (1.f - ks.z) * albedo.z);
     }
-    const float wpx = 2.f * __fdividef(1.f, px);                             // main.cpp:780
+    const float wpx = 2.f * pt_fdiv(1.f, px);                             // main.cpp:780
     beta = f3(beta.x * wpx * brdf.x, beta.y * wpx * brdf.y, beta.z * wpx * brdf.z);
     o = P;
     d = L;

@@ -30,7 +30,7 @@ __device__ __forceinline__ float pt_sphere_t(float3 o, float3 d, float a, float4
 __device__ __forceinline__ float pt_plane_t(float3 o, float3 d, float4 p) {
     float denom = dot3(p, d);
     if (!((denom < -PT_TOLERANCE) || (denom > PT_TOLERANCE))) return __int_as_float(0x7fc00000);
-    return __fdividef(p.w - dot3(p, o), denom);
+    return pt_fdiv(p.w - dot3(p, o), denom);
 }
 
 // RayIntersectPlanarShape<TRIANGLE|QUAD>, ray_math.hpp:357-381, on a precomputed PtPlanar record

@@ -1,0 +1,26 @@
+#!/bin/bash
+# First GPU call of the next round: experiments prepared without a GPU at the end of round 1, each checked for
+# bit-identity of every output against the product build (tools/ab_identity.py) and timed.  ~25 s of GPU per line.
+#   1. -DPT_X_BARE_MUFU      bare MUFU.RCP / MUFU.RSQ instead of __fdividef / rsqrtf (80 instructions off k_render<624>)
+#   2. environment sweeps on the product build: PT_SHADE_BATCH x PT_COOP_MAX, PT_TRI_LEAF (the optimum may have moved
+#      now that sparse walks are cooperative)
+# Build the variants HERE (CPU container) before the call: tools/build_flag_variant.sh bare_mufu -DPT_X_BARE_MUFU
+mkdir -p gpurun_out
+python tools/ab_identity.py dump pathtracer_b200/libpt_b200.so gpurun_out/ab_prod.npz > gpurun_out/r02_prod.log 2>&1
+for v in build/libpt_b200_*.so; do
+  [ -e "$v" ] || continue
+  t=$(basename $v .so)
+  python tools/ab_identity.py dump $v gpurun_out/ab_$t.npz > gpurun_out/r02_$t.log 2>&1
+  python tools/ab_identity.py compare gpurun_out/ab_prod.npz gpurun_out/ab_$t.npz | tee gpurun_out/r02_compare_$t.json
+  rm -f gpurun_out/ab_$t.npz
+done
+rm -f gpurun_out/ab_prod.npz
+for sb in 12 16 20 24 28 32; do for cm in 8 12 16; do
+  echo "shade_batch=$sb coop_max=$cm: $(PT_SHADE_BATCH=$sb PT_COOP_MAX=$cm python tools/profile_render.py --world 5 --pp 16 --frames 3 | tail -1)"
+done; done | tee gpurun_out/r02_sweep_shade_coop.txt
+for leaf in 2 3 4 6 8; do
+  echo "tri_leaf=$leaf: $(PT_TRI_LEAF=$leaf python tools/profile_render.py --world 5 --pp 16 --frames 3 | tail -1)"
+done | tee gpurun_out/r02_sweep_tri_leaf.txt
+for l in 1 2 3 4 5; do
+  echo "sample_lanes_log2=$l: $(PT_SAMPLE_LANES_LOG2=$l python tools/profile_render.py --world 5 --pp 16 --frames 3 | tail -1)"
+done | tee gpurun_out/r02_sweep_lanes.txt
