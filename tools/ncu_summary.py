@@ -29,6 +29,35 @@ def main():
         for i, h in enumerate(hdr):
             if h in KEYS or h.startswith("smsp__average_warps_issue_stalled") and h.endswith("per_issue_active.ratio"):
                 lines.append(f"{h:90s} {krow[i]:>18s} {units[i]}")
+        # derived: achieved bandwidths of the memory levels (sectors are 32 bytes) and where the L1 traffic comes from
+        def val(name):
+            for i, h in enumerate(hdr):                      # some columns carry a section prefix ("SM_B.TriageCompute.<metric>")
+                if h == name or h.endswith("." + name):
+                    try:
+                        return float(krow[i].replace(",", ""))
+                    except ValueError:
+                        pass
+            return None
+        dur = val("gpu__time_duration.sum")
+        if dur:
+            dur_s = dur * {"ns": 1e-9, "us": 1e-6, "ms": 1e-3, "s": 1.0}.get(units[hdr.index("gpu__time_duration.sum")], 1e-9)
+            l1, l2 = val("l1tex__t_sectors.sum"), val("lts__t_sectors.sum")
+            g_ld = val("l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum")
+            l_ld, l_st = val("l1tex__t_sectors_pipe_lsu_mem_local_op_ld.sum"), val("l1tex__t_sectors_pipe_lsu_mem_local_op_st.sum")
+            dr, dw = val("dram__bytes_read.sum"), val("dram__bytes_write.sum")
+            lines.append("-- derived (32-byte sectors / kernel duration)")
+            if l1: lines.append(f"L1 (l1tex) achieved                {l1 * 32 / dur_s / 1e9:10.1f} GB/s   ({l1 * 32 / 1e9:.2f} GB per launch)")
+            if g_ld: lines.append(f"  global loads (BVH nodes, triangle records, materials)  {g_ld * 32 / dur_s / 1e9:10.1f} GB/s, all but {100 - (val('l1tex__t_sector_pipe_lsu_mem_global_op_ld_hit_rate.pct') or 0):.2f} % served by L1")
+            if l_ld is not None and l_st is not None: lines.append(f"  local loads / stores (traversal stack, per-lane sums, spills)  {l_ld * 32 / dur_s / 1e9:10.1f} / {l_st * 32 / dur_s / 1e9:.1f} GB/s (stores write through to L2)")
+            if l2: lines.append(f"L2 (lts) achieved                  {l2 * 32 / dur_s / 1e9:10.1f} GB/s")
+            if dr is not None and dw is not None:
+                scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+                b = dr * scale.get(units[hdr.index("dram__bytes_read.sum")], 1.0) + dw * scale.get(units[hdr.index("dram__bytes_write.sum")], 1.0)
+                lines.append(f"HBM (dram) achieved                {b / dur_s / 1e9:10.1f} GB/s   ({b / 1e6:.1f} MB per launch)")
+            wee = val("smsp__thread_inst_executed_per_inst_executed.ratio")
+            if wee: lines.append(f"warp execution efficiency          {100 * wee / 32:10.1f} %   (active threads per instruction / 32)")
+            be = val("smsp__sass_average_branch_targets_threads_uniform.pct")
+            if be: lines.append(f"branch efficiency                  {be:10.1f} %   (branch targets uniform across the warp)")
     src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--print-source", "cuda,sass", "--csv"], capture_output=True, text=True).stdout
     cur, agg = None, []
     for r in csv.reader(src.splitlines()):

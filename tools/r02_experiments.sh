@@ -4,7 +4,10 @@
 #   1. -DPT_X_BARE_MUFU      bare MUFU.RCP / MUFU.RSQ instead of __fdividef / rsqrtf (80 instructions off k_render<624>)
 #   2. environment sweeps on the product build: PT_SHADE_BATCH x PT_COOP_MAX, PT_TRI_LEAF (the optimum may have moved
 #      now that sparse walks are cooperative)
-# Build the variants HERE (CPU container) before the call: tools/build_flag_variant.sh bare_mufu -DPT_X_BARE_MUFU
+#   3. -DPT_RENDER_MIN_BLOCKS=7 / 6: fewer CTAs per SM for the triangle family (spills 116 -> 52 -> 8 bytes); read w5 only,
+#      the flag caps every variant
+# Build the variants HERE (CPU container) before the call:
+#   tools/build_flag_variant.sh bare_mufu -DPT_X_BARE_MUFU; tools/build_flag_variant.sh mb7 -DPT_RENDER_MIN_BLOCKS=7; tools/build_flag_variant.sh mb6 -DPT_RENDER_MIN_BLOCKS=6
 mkdir -p gpurun_out
 python tools/ab_identity.py dump pathtracer_b200/libpt_b200.so gpurun_out/ab_prod.npz > gpurun_out/r02_prod.log 2>&1
 for v in build/libpt_b200_*.so; do
