@@ -84,6 +84,8 @@ extern "C" int pt_api_version(void) { return PT_API_VERSION; }
 
 extern "C" const char *pt_last_error(const pt_context *ctx) { return ctx ? ctx->error.c_str() : g_create_error.c_str(); }
 
+extern "C" int pt_destroy(pt_context *ctx);
+
 extern "C" int pt_create(const pt_config *cfg, pt_context **out) {
     if (!out) return fail(nullptr, PT_ERR_INVALID_ARG, "pt_create: out is NULL");
     *out = nullptr;
@@ -108,9 +110,17 @@ extern "C" int pt_create(const pt_config *cfg, pt_context **out) {
         if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return fail(nullptr, PT_ERR_CUDA, "cudaStreamCreate failed"); }
         ctx->own_stream = true;
     }
-    cudaEventCreate(&ctx->ev0);
-    cudaEventCreate(&ctx->ev1);
-    if (cudaMalloc(&ctx->counters, PT_N_COUNTERS * sizeof(unsigned long long)) != cudaSuccess) { delete ctx; return fail(nullptr, PT_ERR_OOM, "cudaMalloc failed"); }
+    // from here on a failure releases what exists through pt_destroy (stream, events, counters)
+    if (cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess) {
+        cudaGetLastError();
+        pt_destroy(ctx);
+        return fail(nullptr, PT_ERR_CUDA, "cudaEventCreate failed");
+    }
+    if (cudaMalloc(&ctx->counters, PT_N_COUNTERS * sizeof(unsigned long long)) != cudaSuccess) {
+        cudaGetLastError();
+        pt_destroy(ctx);
+        return fail(nullptr, PT_ERR_OOM, "cudaMalloc failed");
+    }
     cudaMemset(ctx->counters, 0, PT_N_COUNTERS * sizeof(unsigned long long));
     if (const char *s = getenv("PT_SAMPLE_LANES_LOG2")) ctx->sample_lanes_log2 = atoi(s);
     if (const char *s = getenv("PT_SHADE_BATCH")) ctx->shade_batch = atoi(s);
@@ -266,6 +276,10 @@ extern "C" int pt_upload_scene(pt_context *ctx, const pt_scene *s) {
     if (s->n_materials == 0 || !s->materials) return fail(ctx, PT_ERR_INVALID_ARG, "pt_upload_scene: material 0 (the sky) is required");
     if (s->n_spheres == 0 && !(s->flags & PT_SCENE_JUST_COSINE))
         return fail(ctx, PT_ERR_INVALID_ARG, "pt_upload_scene: spheres[0] (the sampled light) is required unless JUST_COSINE");
+    if ((s->n_spheres && !s->spheres) || (s->n_planes && !s->planes) || (s->n_quads && !s->quads) || (s->n_aabbs && !s->aabbs) ||
+        (s->n_triangles && (!s->tri_points || !s->tri_materials)))
+        return fail(ctx, PT_ERR_INVALID_ARG, "pt_upload_scene: a primitive count is non-zero but its array is NULL");
+    if (s->n_triangles >= (1u << 24)) return fail(ctx, PT_ERR_UNSUPPORTED, "pt_upload_scene: more than 2^24 - 1 triangles (leaf links hold 24-bit positions)");
     CK(cudaSetDevice(ctx->device));
     CK(cudaStreamSynchronize(ctx->stream));
     free_scene(ctx);
