@@ -345,7 +345,7 @@ extern "C" int pt_upload_scene(pt_context *ctx, const pt_scene *s) {
         ptbvh::Result r;
         if (ctx->bvh_builder == PT_BVH_DEVICE_LBVH) { if ((rc = pt_lbvh_build(ctx->stream, boxes, ctx->sph_leaf, r, ctx->error))) return rc; }
         else r = ptbvh::Builder(boxes, ctx->sph_leaf, ctx->sah_sweep).build();
-        if (r.max_depth > PT_STACK_DEPTH - 2) return fail(ctx, PT_ERR_UNSUPPORTED, "sphere BVH deeper than the traversal stack");
+        if (r.max_depth > PT_WALK_STACK_LIMIT - 2) return fail(ctx, PT_ERR_UNSUPPORTED, "sphere BVH deeper than the traversal stack");
         std::vector<float4> ordered(r.order.size());
         std::vector<uint32_t> ids(r.order.size());
         for (size_t i = 0; i < r.order.size(); i++) { ordered[i] = bvh_sph_src[r.order[i]]; ids[i] = bvh_src_ids[r.order[i]]; }
@@ -389,7 +389,7 @@ extern "C" int pt_upload_scene(pt_context *ctx, const pt_scene *s) {
         ptbvh::Result r;
         if (ctx->bvh_builder == PT_BVH_DEVICE_LBVH) { if ((rc = pt_lbvh_build(ctx->stream, boxes, ctx->tri_leaf, r, ctx->error))) return rc; }
         else r = ptbvh::Builder(boxes, ctx->tri_leaf, ctx->sah_sweep).build();
-        if (r.max_depth > PT_STACK_DEPTH - 2) return fail(ctx, PT_ERR_UNSUPPORTED, "triangle BVH deeper than the traversal stack");
+        if (r.max_depth > PT_WALK_STACK_LIMIT - 2) return fail(ctx, PT_ERR_UNSUPPORTED, "triangle BVH deeper than the traversal stack");
         std::vector<PtPlanar> ordered(r.order.size());
         for (size_t i = 0; i < r.order.size(); i++) ordered[i] = recs[r.order[i]];
         if ((rc = upload(ctx, ordered, &D.tris)) || (rc = upload(ctx, r.order, &D.tri_ids)) || (rc = upload(ctx, normals, &D.tri_normals)) ||

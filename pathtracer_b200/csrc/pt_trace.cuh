@@ -76,6 +76,21 @@ __device__ __forceinline__ void pt_accept(PtHit &h, float t, uint32_t id) {
 enum { PT_LEAF_SPHERES = 0, PT_LEAF_TRIS = 1 };
 #define PT_STACK_SENTINEL ((int)0x80000000)
 
+// The per-lane traversal stack.  Default: a thread-local array (local memory: L1-resident, stores write through to L2).
+// -DPT_X_SMEM_STACK (experiment build, tools/r02_experiments.sh): one column per thread of a shared-memory array, 32
+// entries deep (16 KB per 128-thread CTA; pt_upload_scene of that build rejects deeper trees), conflict-free.
+#ifdef PT_X_SMEM_STACK
+#define PT_X_SMEM_STACK_DEPTH 32
+__shared__ int pt_s_stack[PT_X_SMEM_STACK_DEPTH][128];      // one array per kernel, whichever walks it inlines (all launch 128 threads)
+#define PT_DECLARE_STACK
+#define PT_STK(i) pt_s_stack[(i)][threadIdx.x & 127u]
+#define PT_WALK_STACK_LIMIT PT_X_SMEM_STACK_DEPTH
+#else
+#define PT_DECLARE_STACK int stack[PT_STACK_DEPTH]
+#define PT_STK(i) stack[(i)]
+#define PT_WALK_STACK_LIMIT PT_STACK_DEPTH
+#endif
+
 __device__ __forceinline__ float pt_rcp_approx(float x) {
     float r;
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
@@ -159,8 +174,8 @@ __device__ __forceinline__ void pt_bvh_walk(const PtDeviceScene &S, const PtBvh 
     const uint32_t n_enter = __popc(__ballot_sync(__activemask(), enters));
     uint32_t my_steps = 0;
 #endif
-    int stack[PT_STACK_DEPTH];
-    stack[0] = PT_STACK_SENTINEL;
+    PT_DECLARE_STACK;
+    PT_STK(0) = PT_STACK_SENTINEL;
     int sp = 1;
     int node = 0;
     const float4 *nodes = reinterpret_cast<const float4 *>(bvh.nodes);
@@ -176,15 +191,15 @@ __device__ __forceinline__ void pt_bvh_walk(const PtDeviceScene &S, const PtBvh 
             pt_node_slabs(b0, b1, b2, r, h.t, hl, hr, ln, rn);
             if (hl && hr) {
                 bool left_first = ln <= rn;
-                stack[sp++] = left_first ? link.y : link.x;
+                PT_STK(sp++) = left_first ? link.y : link.x;
                 node = left_first ? link.x : link.y;
             } else if (hl) node = link.x;
             else if (hr) node = link.y;
-            else node = stack[--sp];
+            else node = PT_STK(--sp);
         }
         if (node != PT_STACK_SENTINEL) {
             pt_leaf_test<LEAF>(S, node, o, d, a, h);
-            node = stack[--sp];
+            node = PT_STK(--sp);
         }
     }
 #ifdef PT_STATS_HIST
@@ -260,10 +275,10 @@ __device__ __forceinline__ void pt_bvh_root_step(const PtBvh &bvh, const PtRayIn
 template <int LEAF>
 __device__ __forceinline__ void pt_bvh_walk_from(const PtDeviceScene &S, const PtBvh &bvh, const PtRayInv &r, float3 o, float3 d, float a,
                                                  PtHit &h, int node, int far) {
-    int stack[PT_STACK_DEPTH];
-    stack[0] = PT_STACK_SENTINEL;
+    PT_DECLARE_STACK;
+    PT_STK(0) = PT_STACK_SENTINEL;
     int sp = 1;
-    if (far != PT_STACK_SENTINEL) stack[sp++] = far;
+    if (far != PT_STACK_SENTINEL) PT_STK(sp++) = far;
     const float4 *nodes = reinterpret_cast<const float4 *>(bvh.nodes);
     while (node != PT_STACK_SENTINEL) {
         while (node >= 0) {
@@ -274,15 +289,15 @@ __device__ __forceinline__ void pt_bvh_walk_from(const PtDeviceScene &S, const P
             pt_node_slabs(b0, b1, b2, r, h.t, hl, hr, ln, rn);
             if (hl && hr) {
                 bool left_first = ln <= rn;
-                stack[sp++] = left_first ? link.y : link.x;
+                PT_STK(sp++) = left_first ? link.y : link.x;
                 node = left_first ? link.x : link.y;
             } else if (hl) node = link.x;
             else if (hr) node = link.y;
-            else node = stack[--sp];
+            else node = PT_STK(--sp);
         }
         if (node != PT_STACK_SENTINEL) {
             pt_leaf_test<LEAF>(S, node, o, d, a, h);
-            node = stack[--sp];
+            node = PT_STK(--sp);
         }
     }
 }

@@ -6,7 +6,9 @@
 #      now that sparse walks are cooperative)
 #   3. -DPT_RENDER_MIN_BLOCKS=7 / 6: fewer CTAs per SM for the triangle family (spills 116 -> 52 -> 8 bytes); read w5 only,
 #      the flag caps every variant
-# Build the variants HERE (CPU container) before the call:
+#   4. -DPT_X_SMEM_STACK: per-lane traversal stack in shared memory (16 KB per CTA) instead of local memory -- local
+#      memory is half of the L1 traffic and all of the L2 traffic of k_render (profiles/r01h_k_render_*_summary.txt)
+# Build the variants HERE (CPU container) before the call (tools/build_flag_variant.sh smem_stack -DPT_X_SMEM_STACK; ...):
 #   tools/build_flag_variant.sh bare_mufu -DPT_X_BARE_MUFU; tools/build_flag_variant.sh mb7 -DPT_RENDER_MIN_BLOCKS=7; tools/build_flag_variant.sh mb6 -DPT_RENDER_MIN_BLOCKS=6
 mkdir -p gpurun_out
 python tools/ab_identity.py dump pathtracer_b200/libpt_b200.so gpurun_out/ab_prod.npz > gpurun_out/r02_prod.log 2>&1
