@@ -41,7 +41,7 @@ def parse():
     ap.add_argument("--pp", type=int, default=32)
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
-    ap.add_argument("--shard", default="tiles", choices=["tiles", "samples"])
+    ap.add_argument("--shard", default="tiles", choices=["tiles", "samples", "tiles_p2p"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--kernel", default="auto", choices=["auto", "mega", "wavefront"])
     return ap.parse_args()
@@ -231,7 +231,7 @@ def run_b200(a):
     # the dominant kernel alone (k_render of this rank's share), events on its launch stream
     kms = []
     for i in range(a.steps):
-        if a.shard == "tiles":
+        if a.shard in ("tiles", "tiles_p2p"):
             core.render(a.width, a.height, a.pp, seed=1 + i, tile_rank=rank, tile_count=world)
         else:
             lo, hi = D.sample_range(a.pp, rank, world)

@@ -217,6 +217,22 @@ int pt_unpack_tiles(pt_context *ctx, const void *src_dev, uint32_t tile_rank, ui
 int pt_gather_tiles_from(pt_context *dst, pt_context *src, uint32_t tile_rank, uint32_t tile_count);
 int pt_add_accum_from(pt_context *dst, pt_context *src);
 
+/* One process per GPU, direct tile exchange over NVLink peer memory (the fused "resolve + gather"): the root rank exports
+ * its BGRA frame as a CUDA IPC handle, every other rank maps it, and pt_resolve_tiles_to resolves THIS rank's tiles
+ * {t : t % tile_count == tile_rank} and stores the BGRA words straight into the mapped frame (one 128-byte row segment of a
+ * tile per warp) -- no pack, no NCCL gather, no unpack.  The caller orders the ranks (a stream-ordered all-reduce of one
+ * word before and after; pathtracer_b200/dist.py, mode "tiles_p2p").  No reference counterpart: the reference's worker
+ * threads write their tiles into the one shared g_image (main.cpp:107, 862-866) -- this is that, across GPUs.
+ *   pt_frame_ipc_handle : allocate the width x height frame if needed; write the PT_IPC_HANDLE_BYTES blob of its BGRA buffer.
+ *                         The handle dies with the frame (a pt_render at another size re-allocates it).
+ *   pt_open_peer_frame  : map another process's frame; *remote_bgra is a device pointer valid in this process.
+ *   pt_resolve_tiles_to : dst_bgra = NULL resolves into the context's own frame. */
+#define PT_IPC_HANDLE_BYTES 72        /* cudaIpcMemHandle_t (64) + the frame's byte offset inside the exported allocation (8) */
+int pt_frame_ipc_handle(pt_context *ctx, int32_t width, int32_t height, void *handle_out);
+int pt_open_peer_frame(pt_context *ctx, const void *handle, void **remote_bgra);
+int pt_close_peer_frame(pt_context *ctx, void *remote_bgra);
+int pt_resolve_tiles_to(pt_context *ctx, void *dst_bgra, uint32_t tile_rank, uint32_t tile_count);
+
 /* debug / parity exports */
 /* closest hit of n caller-supplied rays (origins, dirs: n*3 floats, host pointers) */
 int pt_trace_rays(pt_context *ctx, uint32_t n, const float *origins, const float *dirs, pt_hit *hits_out);

@@ -7,6 +7,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "pt_api.h"
@@ -60,6 +61,7 @@ struct pt_context {
     size_t pack_bytes = 0, stage_bytes = 0;
     cudaEvent_t ev_sent = nullptr, ev_stage_free = nullptr;
     bool stage_in_use = false;
+    std::vector<std::pair<void *, void *>> peer_maps;   // pt_open_peer_frame: (frame pointer, base of the mapped allocation)
     void *flush_buf = nullptr;                 // pt_flush_l2
     size_t flush_bytes = 0;
     int flush_value = 0;
@@ -157,6 +159,8 @@ extern "C" int pt_destroy(pt_context *ctx) {
     free_scene(ctx);
     free_frame(ctx);
     ctx->wf.release();
+    for (auto &m : ctx->peer_maps) cudaIpcCloseMemHandle(m.second);
+    ctx->peer_maps.clear();
     if (ctx->counters) cudaFree(ctx->counters);
     if (ctx->pack_buf) cudaFree(ctx->pack_buf);
     if (ctx->flush_buf) cudaFree(ctx->flush_buf);
@@ -631,6 +635,79 @@ extern "C" int pt_unpack_tiles(pt_context *ctx, const void *src, uint32_t rank, 
     uint32_t n = my_tile_count(tiles_x * tiles_y, rank, count);
     if (n) k_unpack_tiles<<<(n * 1024u + 255u) / 256u, 256, 0, ctx->stream>>>(ctx->bgra, (const uint32_t *)src, ctx->width, ctx->height, tiles_x, rank, count, n);
     CK(cudaGetLastError());
+    return PT_OK;
+}
+
+// ---- one process per GPU: tiles resolved straight into the root rank's frame over NVLink peer memory ----------
+// An IPC handle names the whole driver allocation a pointer lives in (small cudaMallocs are carved out of shared slabs), and
+// opening it yields that allocation's base: the blob handed to the peers is therefore handle + offset of the frame in it.
+// cuMemGetAddressRange comes through the runtime's entry-point query, so the library does not link against libcuda.
+static size_t offset_in_allocation(const void *p) {
+    void *fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuMemGetAddressRange", &fn, cudaEnableDefault, &q) != cudaSuccess || !fn) { cudaGetLastError(); return 0; }
+    typedef int (*range_fn)(unsigned long long *, size_t *, unsigned long long);
+    unsigned long long base = 0;
+    size_t size = 0;
+    if (((range_fn)fn)(&base, &size, (unsigned long long)(uintptr_t)p) != 0 || base == 0) return 0;
+    return (size_t)((unsigned long long)(uintptr_t)p - base);
+}
+
+extern "C" int pt_frame_ipc_handle(pt_context *ctx, int32_t width, int32_t height, void *handle_out) {
+    static_assert(sizeof(cudaIpcMemHandle_t) + sizeof(uint64_t) == PT_IPC_HANDLE_BYTES, "PT_IPC_HANDLE_BYTES = cudaIpcMemHandle_t + offset");
+    if (!ctx || !handle_out || width <= 0 || height <= 0) return PT_ERR_INVALID_ARG;
+    CK(cudaSetDevice(ctx->device));
+    int rc = ensure_frame(ctx, width, height);
+    if (rc) return rc;
+    cudaIpcMemHandle_t h;
+    CK(cudaIpcGetMemHandle(&h, ctx->bgra));
+    const uint64_t off = (uint64_t)offset_in_allocation(ctx->bgra);
+    memcpy(handle_out, &h, sizeof(h));
+    memcpy((char *)handle_out + sizeof(h), &off, sizeof(off));
+    return PT_OK;
+}
+
+extern "C" int pt_open_peer_frame(pt_context *ctx, const void *handle, void **remote_bgra) {
+    if (!ctx || !handle || !remote_bgra) return PT_ERR_INVALID_ARG;
+    *remote_bgra = nullptr;
+    CK(cudaSetDevice(ctx->device));
+    cudaIpcMemHandle_t h;
+    uint64_t off = 0;
+    memcpy(&h, handle, sizeof(h));
+    memcpy(&off, (const char *)handle + sizeof(h), sizeof(off));
+    void *base = nullptr;
+    CK(cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess));
+    void *p = (char *)base + off;
+    ctx->peer_maps.push_back({p, base});
+    *remote_bgra = p;
+    return PT_OK;
+}
+
+extern "C" int pt_close_peer_frame(pt_context *ctx, void *remote_bgra) {
+    if (!ctx) return PT_ERR_INVALID_ARG;
+    if (!remote_bgra) return PT_OK;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    for (size_t i = 0; i < ctx->peer_maps.size(); i++)
+        if (ctx->peer_maps[i].first == remote_bgra) {
+            void *base = ctx->peer_maps[i].second;
+            ctx->peer_maps.erase(ctx->peer_maps.begin() + i);
+            CK(cudaIpcCloseMemHandle(base));
+            return PT_OK;
+        }
+    return fail(ctx, PT_ERR_INVALID_ARG, "pt_close_peer_frame: not a frame this context mapped");
+}
+
+extern "C" int pt_resolve_tiles_to(pt_context *ctx, void *dst_bgra, uint32_t rank, uint32_t count) {
+    if (!ctx || count == 0 || rank >= count) return PT_ERR_INVALID_ARG;
+    if (!ctx->accum) return fail(ctx, PT_ERR_NO_FRAME, "pt_resolve_tiles_to: nothing rendered yet");
+    CK(cudaSetDevice(ctx->device));
+    uint32_t tiles_x = (uint32_t)(ctx->width + PT_TILE - 1) / PT_TILE, tiles_y = (uint32_t)(ctx->height + PT_TILE - 1) / PT_TILE;
+    uint32_t n = my_tile_count(tiles_x * tiles_y, rank, count);
+    uint32_t *dst = dst_bgra ? (uint32_t *)dst_bgra : ctx->bgra;
+    if (n) k_resolve_tiles_to<<<(n * 1024u + 255u) / 256u, 256, 0, ctx->stream>>>(ctx->accum, dst, ctx->width, ctx->height, tiles_x, rank, count, n);
+    CK(cudaGetLastError());
+    if (!dst_bgra) ctx->resolved = true;       // own frame: the caller vouches that peers fill the other ranks' tiles (pt_readback must not re-resolve)
     return PT_OK;
 }
 

@@ -492,6 +492,21 @@ __global__ void k_unpack_tiles(uint32_t *__restrict__ bgra, const uint32_t *__re
     if (x < W && y < H) bgra[(size_t)y * W + x] = packed[i];
 }
 
+// resolve this rank's tiles straight into a BGRA frame that may live on another GPU (mapped peer memory): thread i
+// handles pixel i & 1023 of own tile i >> 10, so a warp stores one 128-byte row segment of a tile
+__global__ void k_resolve_tiles_to(const float4 *__restrict__ accum, uint32_t *__restrict__ dst, int W, int H,
+                                   uint32_t tiles_x, uint32_t rank, uint32_t count, uint32_t n_my_tiles) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_my_tiles * 1024u) return;
+    uint32_t j = i >> 10, p = i & 1023u;
+    uint32_t tile = rank + j * count;
+    int x = (int)((tile % tiles_x) * PT_TILE + (p & 31u)), y = (int)((tile / tiles_x) * PT_TILE + (p >> 5));
+    if (x >= W || y >= H) return;
+    float4 a = accum[(size_t)y * W + x];
+    float inv = a.w > 0.f ? __fdiv_rn(1.0f, a.w) : 0.f;
+    dst[(size_t)y * W + x] = pt_resolve_pixel(__fmul_rn(a.x, inv), __fmul_rn(a.y, inv), __fmul_rn(a.z, inv));
+}
+
 // ---- FP32 roofline probe: 8 independent FMA chains per thread ------------------------------------------
 __global__ void k_fma_peak(float *out, int iters) {
     float a[8];

@@ -10,6 +10,14 @@ The reference's only parallelism is CPU threads over 32x32 tiles handed out by M
   * "samples" rank r renders samples [r*spp/G, (r+1)*spp/G) of every pixel into its float4
               accumulation buffer; one REDUCE(sum, fp32) to rank 0, which resolves.
 
+  * "tiles_p2p" the same partition as "tiles", exchanged without a collective on the data path: rank 0 exports
+              its BGRA frame as a CUDA IPC handle once, the other ranks map it, and every rank's resolve kernel
+              stores its tiles straight into that frame over NVLink (pt_resolve_tiles_to) -- resolve + pack +
+              gather + unpack become one kernel per rank.  Two stream-ordered one-word all-reduces per frame
+              order the ranks: (A) rank 0 has finished with the previous frame, (B) every rank's tiles have landed.
+              (CUDA only: written at the end of round 1 without a GPU at hand, opt-in until tools/p2p_check.py has
+              run on a multi-GPU box.)
+
 The collectives run on torch tensors, so the same code runs on NCCL (GPU) and on gloo (CPU tests,
 where the render step is injected).  Nothing here does render arithmetic.
 """
@@ -102,11 +110,48 @@ class ShardedFrame:
         self.torch = torch
         self._packed = None
         self.launches = 0
+        self._remote = None          # tiles_p2p: rank 0's frame mapped into this process
+        self._flag = None
+
+    def _p2p_setup(self):
+        """Once per frame size: rank 0 exports its BGRA frame, everybody else maps it."""
+        import torch.distributed as dist
+        torch, core = self.torch, self.core
+        self._flag = torch.zeros(1, dtype=torch.int32, device="cuda")
+        h = torch.zeros(72, dtype=torch.uint8, device="cuda")      # PT_IPC_HANDLE_BYTES
+        if self.rank == 0:
+            raw = core.frame_ipc_handle(self.w, self.h)
+            h.copy_(torch.frombuffer(bytearray(raw), dtype=torch.uint8))
+        if self.world > 1:
+            dist.broadcast(h, src=0, group=self.group)
+            if self.rank != 0:
+                self._remote = core.open_peer_frame(bytes(h.cpu().numpy().tobytes()))
+        self._p2p_ready = True
+
+    def close(self):
+        if self._remote:
+            self.core.close_peer_frame(self._remote)
+            self._remote = None
 
     def render(self, pp, seed):
         """Returns rank 0's resolved BGRA frame as a device int32 tensor [H, W] (None on other ranks)."""
         torch, core = self.torch, self.core
         self.launches = 0
+        if self.mode == "tiles_p2p":
+            import torch.distributed as dist
+            if not getattr(self, "_p2p_ready", False):
+                self._p2p_setup()
+            core.render(self.w, self.h, pp, seed=seed, tile_rank=self.rank, tile_count=self.world)
+            if self.world > 1:
+                dist.all_reduce(self._flag, group=self.group)      # (A) rank 0's stream is past everything that read the previous frame
+            core.resolve_tiles_to(self._remote if self.rank != 0 else None, self.rank, self.world)
+            self.launches += 2
+            if self.world > 1:
+                dist.all_reduce(self._flag, group=self.group)      # (B) ordered after every rank's stores on its stream
+            if self.rank != 0:
+                return None
+            _, b = core.device_buffers()
+            return torch.as_tensor(b, device="cuda")
         if self.mode == "tiles":
             core.render(self.w, self.h, pp, seed=seed, tile_rank=self.rank, tile_count=self.world)
             core.resolve()

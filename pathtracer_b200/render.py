@@ -15,6 +15,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # PT_B200_LIB: another build of the same library (kernel experiments: tools/build_variants.sh)
 LIB_PATH = os.environ.get("PT_B200_LIB") or os.path.join(_HERE, "libpt_b200.so")
 
+IPC_HANDLE_BYTES = 72       # PT_IPC_HANDLE_BYTES
 _lib = None
 
 
@@ -49,6 +50,10 @@ def lib():
         L.pt_add_accum_from.argtypes = [C.c_void_p, C.c_void_p]
         L.pt_pack_tiles.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint32)]
         L.pt_unpack_tiles.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]
+        L.pt_frame_ipc_handle.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]
+        L.pt_open_peer_frame.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p)]
+        L.pt_close_peer_frame.argtypes = [C.c_void_p, C.c_void_p]
+        L.pt_resolve_tiles_to.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]
         L.pt_trace_rays.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]
         L.pt_primary_hits.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]
         L.pt_trace_paths.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
@@ -61,7 +66,8 @@ def lib():
 EXPORTS = ["pt_api_version", "pt_create", "pt_destroy", "pt_last_error", "pt_upload_scene", "pt_set_camera",
            "pt_render", "pt_synchronize", "pt_resolve", "pt_readback", "pt_device_buffers", "pt_set_stream",
            "pt_pack_tiles", "pt_unpack_tiles", "pt_gather_tiles_from", "pt_add_accum_from", "pt_trace_rays", "pt_primary_hits", "pt_trace_paths",
-           "pt_resolve_colors", "pt_measure_fp32_peak", "pt_flush_l2"]
+           "pt_resolve_colors", "pt_measure_fp32_peak", "pt_flush_l2",
+           "pt_frame_ipc_handle", "pt_open_peer_frame", "pt_close_peer_frame", "pt_resolve_tiles_to"]
 
 
 def _p(a):
@@ -159,6 +165,27 @@ class RenderCore:
     def add_accum_from(self, src):
         """Single-process multi-GPU: accum += src.accum (sample-range sharding)."""
         self._ck(lib().pt_add_accum_from(self._h, src._h))
+
+    # ---- direct tile exchange over peer memory (one process per GPU) ----
+    def frame_ipc_handle(self, width, height):
+        """PT_IPC_HANDLE_BYTES blob naming this context's BGRA frame (allocated here if needed)."""
+        buf = (C.c_uint8 * IPC_HANDLE_BYTES)()
+        self._ck(lib().pt_frame_ipc_handle(self._h, width, height, buf))
+        self.width, self.height = width, height
+        return bytes(buf)
+
+    def open_peer_frame(self, handle):
+        p = C.c_void_p()
+        buf = (C.c_uint8 * IPC_HANDLE_BYTES).from_buffer_copy(handle)
+        self._ck(lib().pt_open_peer_frame(self._h, buf, C.byref(p)))
+        return p.value
+
+    def close_peer_frame(self, remote):
+        self._ck(lib().pt_close_peer_frame(self._h, remote))
+
+    def resolve_tiles_to(self, dst_ptr, tile_rank, tile_count):
+        """Resolve this rank's tiles into dst_ptr (a mapped peer frame) or, with None, into the own frame."""
+        self._ck(lib().pt_resolve_tiles_to(self._h, dst_ptr, tile_rank, tile_count))
 
     # ---- parity / debug exports ----
     def trace_rays(self, o, d):
