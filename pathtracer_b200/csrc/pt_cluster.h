@@ -56,21 +56,55 @@ inline Box child_box(const Node &n, int side) {
     return b;
 }
 
-// primitive range below `link`; false when it is not one contiguous run of leaf-order positions
-inline bool subtree_range(const Result &r, int32_t link, uint32_t &first, uint32_t &count, int depth = 0) {
-    if (link < 0) {
-        uint32_t enc = (uint32_t)(~link);
-        first = enc & 0xFFFFFFu; count = enc >> 24;
+// Primitive ranges of every inner node, computed once (post-order, iterative): ranges[i] = positions below nodes[i];
+// ok = false when some subtree is not one contiguous run of leaf-order positions (then the tree has no cut).
+struct Ranges {
+    std::vector<uint32_t> first, count;
+    bool ok = true;
+    bool of_link(int32_t link, uint32_t &f, uint32_t &c) const {
+        if (link < 0) {
+            uint32_t enc = (uint32_t)(~link);
+            f = enc & 0xFFFFFFu; c = enc >> 24;
+            return true;
+        }
+        if ((size_t)link >= first.size()) return false;
+        f = first[link]; c = count[link];
         return true;
     }
-    if (depth > 64 || (size_t)link >= r.nodes.size()) return false;
-    uint32_t f0, c0, f1, c1;
-    if (!subtree_range(r, r.nodes[link].link[0], f0, c0, depth + 1) || !subtree_range(r, r.nodes[link].link[1], f1, c1, depth + 1)) return false;
-    if (c0 == 0) { first = f1; count = c1; return true; }
-    if (c1 == 0) { first = f0; count = c0; return true; }
-    if (f0 + c0 == f1) { first = f0; count = c0 + c1; return true; }
-    if (f1 + c1 == f0) { first = f1; count = c0 + c1; return true; }
-    return false;
+};
+
+inline Ranges node_ranges(const Result &r) {
+    Ranges R;
+    const size_t n = r.nodes.size();
+    R.first.assign(n, 0); R.count.assign(n, 0);
+    std::vector<uint8_t> state(n, 0);                 // 0 = unseen, 1 = children pushed, 2 = done
+    std::vector<int32_t> stack;
+    if (n) stack.push_back(0);
+    while (!stack.empty() && R.ok) {
+        const int32_t i = stack.back();
+        if (state[i] == 2) { stack.pop_back(); continue; }
+        if (state[i] == 0) {
+            state[i] = 1;
+            for (int side = 0; side < 2; side++) {
+                const int32_t l = r.nodes[i].link[side];
+                if (l >= 0) {
+                    if ((size_t)l >= n || state[l] != 0) { R.ok = false; break; }      // not a tree
+                    stack.push_back(l);
+                }
+            }
+            continue;
+        }
+        uint32_t f0, c0, f1, c1;
+        if (!R.of_link(r.nodes[i].link[0], f0, c0) || !R.of_link(r.nodes[i].link[1], f1, c1)) { R.ok = false; break; }
+        if (c0 == 0) { R.first[i] = f1; R.count[i] = c1; }
+        else if (c1 == 0) { R.first[i] = f0; R.count[i] = c0; }
+        else if (f0 + c0 == f1) { R.first[i] = f0; R.count[i] = c0 + c1; }
+        else if (f1 + c1 == f0) { R.first[i] = f1; R.count[i] = c0 + c1; }
+        else R.ok = false;
+        state[i] = 2;
+        stack.pop_back();
+    }
+    return R;
 }
 
 inline float rounds(uint32_t count) { return (float)((count + kClusterLanes - 1) / kClusterLanes); }
@@ -83,12 +117,14 @@ inline ClusterCut build_cut(const Result &r, uint32_t max_rounds_per_cluster = 4
     using namespace detail;
     ClusterCut out;
     if (r.nodes.empty()) return out;
+    const Ranges R = node_ranges(r);
+    if (!R.ok) return out;
     std::vector<CutEntry> cut;
     auto push = [&](const Node &n, int side) -> bool {
         CutEntry e;
         e.box = child_box(n, side);
         e.link = n.link[side];
-        if (!subtree_range(r, e.link, e.first, e.count)) return false;
+        if (!R.of_link(e.link, e.first, e.count)) return false;
         if (e.count) cut.push_back(e);
         return true;
     };
@@ -101,7 +137,7 @@ inline ClusterCut build_cut(const Result &r, uint32_t max_rounds_per_cluster = 4
             if (e.link < 0) continue;
             const Node &n = r.nodes[e.link];
             uint32_t f, c0 = 0, c1 = 0;
-            if (!subtree_range(r, n.link[0], f, c0) || !subtree_range(r, n.link[1], f, c1)) return out;
+            if (!R.of_link(n.link[0], f, c0) || !R.of_link(n.link[1], f, c1)) return out;
             float gain = e.box.area() * rounds(e.count) - child_box(n, 0).area() * rounds(c0) - child_box(n, 1).area() * rounds(c1);
             if (e.count > max_rounds_per_cluster * kClusterLanes) gain = 1e30f + (float)e.count;      // must be opened
             if (gain > best_gain) { best_gain = gain; best = (int)i; }
