@@ -56,6 +56,7 @@ struct pt_context {
     // default: 12 for a triangle tree (w5 +8.4 %), off for a sphere tree (w2 -0.5 %, w4 +0.6 %; profiles/r01h_coop_check.jsonl).
     // PT_COOP_MAX=n overrides it for both kinds of tree (0 = off).
     int coop_max = -1;
+    int min_trace = 1;                         // PT_SHADE_MIN_TRACE, read by -DPT_X_SHADE_RULE builds only
     // single-process multi-GPU (pt_gather_tiles_from / pt_add_accum_from)
     void *pack_buf = nullptr, *stage_buf = nullptr;
     size_t pack_bytes = 0, stage_bytes = 0;
@@ -127,6 +128,7 @@ extern "C" int pt_create(const pt_config *cfg, pt_context **out) {
     if (const char *s = getenv("PT_SAMPLE_LANES_LOG2")) ctx->sample_lanes_log2 = atoi(s);
     if (const char *s = getenv("PT_SHADE_BATCH")) ctx->shade_batch = atoi(s);
     if (const char *s = getenv("PT_COOP_MAX")) ctx->coop_max = std::max(0, std::min(32, atoi(s)));
+    if (const char *s = getenv("PT_SHADE_MIN_TRACE")) ctx->min_trace = std::max(1, std::min(33, atoi(s)));
     if (const char *s = getenv("PT_SAH_SWEEP")) ctx->sah_sweep = atoi(s) != 0;
     if (const char *s = getenv("PT_TRI_LEAF")) ctx->tri_leaf = std::max(1, std::min(64, atoi(s)));
     if (const char *s = getenv("PT_SPH_LEAF")) ctx->sph_leaf = std::max(1, std::min(64, atoi(s)));
@@ -521,6 +523,7 @@ extern "C" int pt_render(pt_context *ctx, const pt_render_params *p) {
             A.log2_sample_lanes = lS;
             // parked lanes before the BRDF code runs (variants with PT_F_DEFER): measured best 32 with textures, else 20
             A.shade_batch = ctx->shade_batch > 0 ? (uint32_t)ctx->shade_batch : ((ctx->features & PT_F_TEX) ? 32u : 20u);
+            A.min_trace = (uint32_t)ctx->min_trace;
             // cooperative sparse walks only where exactly one tree exists and it has a cluster cut
             const bool one_tree = (ctx->scene.tri_bvh.n_nodes != 0) != (ctx->scene.sphere_bvh.n_nodes != 0);
             const bool has_cut = ctx->scene.tri_bvh.n_nodes ? ctx->scene.n_tri_clusters != 0 : ctx->scene.n_sph_clusters != 0;

@@ -57,6 +57,7 @@ struct PtRenderArgs {
     float4 *accum;                      // width*height: sum r,g,b + number of samples
     unsigned long long *counters;       // [0] rays, [1] NaN retries, [2] samples
     uint32_t coop_max;                  // PT_F_COOP variants: walks entered by <= coop_max lanes are traced cooperatively (last: keeps offsets)
+    uint32_t min_trace;                 // -DPT_X_SHADE_RULE builds only (PT_SHADE_MIN_TRACE, default 1 = the product rule)
 };
 
 // ---- camera (RenderTexel's two sampling loops, src/win32_main.cpp:1032-1170) ----------------------
@@ -311,7 +312,11 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
             __syncwarp();
             const uint32_t nS = __popc(__ballot_sync(0xffffffffu, state == NEED_SHADE && !done));
             const uint32_t nD = __popc(__ballot_sync(0xffffffffu, done && s + Sn < A.s_end));   // lanes that will regenerate
+#ifdef PT_X_SHADE_RULE      // experiment build: also shade when fewer than min_trace lanes would trace in the next iteration (nD == 0 generalised)
+            if (nS >= A.shade_batch || nD < A.min_trace) {
+#else
             if (nS >= A.shade_batch || nD == 0) {
+#endif
                 if (state == NEED_SHADE && !done) {
                     float3 n;
                     uint32_t mat;

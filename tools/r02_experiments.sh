@@ -29,3 +29,10 @@ done | tee gpurun_out/r02_sweep_tri_leaf.txt
 for l in 1 2 3 4 5; do
   echo "sample_lanes_log2=$l: $(PT_SAMPLE_LANES_LOG2=$l python tools/profile_render.py --world 5 --pp 16 --frames 3 | tail -1)"
 done | tee gpurun_out/r02_sweep_lanes.txt
+# 5. -DPT_X_SHADE_RULE build (tools/build_flag_variant.sh shade_rule -DPT_X_SHADE_RULE): shade the parked lanes also when fewer
+#    than PT_SHADE_MIN_TRACE lanes would trace in the next iteration (1 = the product rule "nobody can regenerate")
+if [ -e build/libpt_b200_shade_rule.so ]; then
+  for mt in 1 4 8 12 16; do for sb in 20 32; do
+    echo "min_trace=$mt shade_batch=$sb: $(PT_B200_LIB=build/libpt_b200_shade_rule.so PT_SHADE_MIN_TRACE=$mt PT_SHADE_BATCH=$sb python tools/profile_render.py --world 5 --pp 16 --frames 3 | tail -1)"
+  done; done | tee gpurun_out/r02_sweep_shade_rule.txt
+fi
