@@ -499,6 +499,10 @@ extern "C" int pt_render(pt_context *ctx, const pt_render_params *p) {
     A.tiles_y = (uint32_t)(p->height + PT_TILE - 1) / PT_TILE;
     A.n_my_tiles = my_tile_count(A.tiles_x * A.tiles_y, p->tile_rank, tile_count);
     A.seed = p->seed;
+    for (uint32_t r = 0; r < 10; r++) {
+        A.philox_k[2 * r] = (uint32_t)p->seed + r * 0x9E3779B9u;
+        A.philox_k[2 * r + 1] = (uint32_t)(p->seed >> 32) + r * 0xBB67AE85u;
+    }
     A.accum = ctx->accum;
     A.counters = ctx->counters;
 

@@ -58,6 +58,7 @@ struct PtRenderArgs {
     unsigned long long *counters;       // [0] rays, [1] NaN retries, [2] samples
     uint32_t coop_max;                  // PT_F_COOP variants: walks entered by <= coop_max lanes are traced cooperatively (last: keeps offsets)
     uint32_t min_trace;                 // -DPT_X_SHADE_RULE builds only (PT_SHADE_MIN_TRACE, default 1 = the product rule)
+    uint32_t philox_k[20];              // -DPT_X_PHILOX_KEYS builds only: round keys of the render seed, (k0_r, k1_r) for r = 0..9
 };
 
 // ---- camera (RenderTexel's two sampling loops, src/win32_main.cpp:1032-1170) ----------------------
@@ -107,7 +108,7 @@ __device__ __forceinline__ void pt_camera_ray(const pt_camera &c, const PtPixelC
         // outer film sample ri jittered +-1 pixel, focal point on the focal plane, lens point from the
         // Poisson table at (ri*r2) % 12 (main.cpp:1114-1161)
         const uint32_t ri = __umulhi(s, pp_magic), r2 = s - ri * (uint32_t)pp;
-        uint4 fj = philox4x32_10(0u, pixel, ri, 1u, (uint32_t)seed, (uint32_t)(seed >> 32));
+        uint4 fj = rng.block_of(0u, pixel, ri, 1u);          // rng.init above set the same seed
         float offX = fx + (2.0f * u32_to_unit(fj.x) - 1.0f) * c.half_pixel_w;
         float offY = fy + (2.0f * u32_to_unit(fj.y) - 1.0f) * c.half_pixel_h;
         float3 P = fc + (offX * c.half_film_w) * ax + (offY * c.half_film_h) * ay;
@@ -167,6 +168,9 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
     h.id = PT_ID_MISS;
     PtRng rng;
     rng.init(A.seed, 0, 0, 0);
+#ifdef PT_X_PHILOX_KEYS
+    rng.K = A.philox_k;
+#endif
 
     // Lane states.  Where only ~30 % of the segments continue with a BRDF sample (w1, w5), shading right
     // after the trace runs the longest straight-line code of the kernel at a third of the lanes.  With
