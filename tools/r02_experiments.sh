@@ -10,7 +10,7 @@
 #      memory is half of the L1 traffic and all of the L2 traffic of k_render (profiles/r01h_k_render_*_summary.txt)
 #   6. -DPT_X_PHILOX_KEYS: the ten Philox round keys of the render seed precomputed into the kernel parameters (20 UIADD3 per
 #      block become 5 LDCU.128; -40 instructions in k_render<624>)      tools/build_flag_variant.sh philox_keys -DPT_X_PHILOX_KEYS
-# Build the variants HERE (CPU container) before the call (tools/build_flag_variant.sh smem_stack -DPT_X_SMEM_STACK; ...):
+# Build the variants HERE (CPU container) before the call: tools/r02_build_variants.sh, i.e.
 #   tools/build_flag_variant.sh bare_mufu -DPT_X_BARE_MUFU; tools/build_flag_variant.sh mb7 -DPT_RENDER_MIN_BLOCKS=7; tools/build_flag_variant.sh mb6 -DPT_RENDER_MIN_BLOCKS=6
 mkdir -p gpurun_out
 python tools/ab_identity.py dump pathtracer_b200/libpt_b200.so gpurun_out/ab_prod.npz > gpurun_out/r02_prod.log 2>&1
