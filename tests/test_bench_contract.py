@@ -54,3 +54,22 @@ def test_reference_arm_runs_on_rank_zero_only():
 def test_shard_modes_on_the_command_line():
     r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--shard", "nonsense"], capture_output=True, text=True)
     assert r.returncode != 0 and "tiles_p2p" in r.stderr
+
+
+def test_ab_identity_compare_reports_differences(tmp_path):
+    """tools/ab_identity.py compare (the gate for adopting an experiment build): identical only if every array is byte-equal."""
+    import numpy as np
+    a, b = str(tmp_path / "a.npz"), str(tmp_path / "b.npz")
+    x = np.arange(12, dtype=np.float32).reshape(3, 4)
+    np.savez(a, acc=x, hits=np.zeros(3, np.uint32))
+    y = x.copy(); y[1, 2] = np.nextafter(y[1, 2], np.float32(100))      # one ulp
+    np.savez(b, acc=y, hits=np.zeros(3, np.uint32))
+    for p in (a, b):
+        json.dump({"w5": {"ms": [1.0, 1.0], "gsamples_per_s": 10.0 if p == a else 11.0}}, open(p + ".times.json", "w"))
+    tool = os.path.join(ROOT, "tools", "ab_identity.py")
+    r = subprocess.run([sys.executable, tool, "compare", a, a], capture_output=True, text=True)
+    assert r.returncode == 0 and json.loads(r.stdout)["identical"] is True
+    r = subprocess.run([sys.executable, tool, "compare", a, b], capture_output=True, text=True)
+    out = json.loads(r.stdout)
+    assert r.returncode == 1 and out["identical"] is False and out["differing"] == ["acc"]
+    assert abs(out["speedup"]["w5"] - 1.1) < 1e-9
