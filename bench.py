@@ -149,21 +149,25 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": int(rows[0][1]), "reasons": reasons, "samples": len(rows)}
 
 
-def ncu_traffic(world):
-    """dram__bytes_read.sum + dram__bytes_write.sum of one k_render launch from the committed `ncu --set full`
-    capture (profiles/k_render_traffic.json; the accumulator is read and written once per launch, so the figure
-    does not depend on spp); None where no capture exists for this world."""
+def ncu_record(world, width, height):
+    """What the committed `ncu --set full` capture of this world's k_render variant measured (profiles/k_render_ncu.json,
+    written by tools/ncu_summary.py, with the commit it profiled): DRAM bytes per launch (the accumulator is read and
+    written once per launch, so the figure scales with the pixel count, not with spp) and EXECUTED FP32 flops per sample
+    (thread-level FADD + FMUL + 2 x FFMA; a property of the code and the scene, not of the clock).  {} where none exists."""
     try:
-        t = json.load(open(os.path.join(ROOT, "profiles", "k_render_traffic.json")))
-        return t.get(f"w{world}", {}).get("dram_bytes_per_launch")
+        t = json.load(open(os.path.join(ROOT, "profiles", "k_render_ncu.json")))
+        r = dict(t.get(f"w{world}", {}))
+        if r and r.get("pixels"):
+            r["dram_bytes_per_launch"] = r["dram_bytes_per_launch"] * (width * height) / r["pixels"]
+        return r
     except Exception:
-        return None
+        return {}
 
 
-def scene_bytes(sc):
+def scene_bytes(sc, textures=True):
     n = sc.n_materials * 68 + sc.n_spheres * 20 + sc.n_planes * 20 + sc.n_quads * 40 + sc.n_aabbs * 52 + sc.n_triangles * 40
     for i in range(4):
-        if sc.textures[i].rgba8:
+        if textures and sc.textures[i].rgba8:
             n += sc.textures[i].width * sc.textures[i].height * 4
     return n + 116
 
@@ -191,6 +195,7 @@ def run_b200(a):
     sc = hw.scene(a.width, a.height)
     core.upload_scene(sc)
     frame = D.ShardedFrame(core, a.width, a.height, a.shard)
+    frame.phase_events = []
     samples_per_step = a.width * a.height * a.pp * a.pp
 
     def barrier():
@@ -208,6 +213,7 @@ def run_b200(a):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     k_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(a.steps)]
     launches = 0
+    frame.phase_events = []
     barrier()
     sampler.mark_begin()
     e0.record()
@@ -227,6 +233,18 @@ def run_b200(a):
     ms_total = float(ms.item())
     step_ms = [round(k_ev[i][0].elapsed_time(k_ev[i][1]), 3) for i in range(a.steps)]
     value = samples_per_step * a.steps / (ms_total * 1e-3) / 1e6
+    # per-phase device times of every rank: render launch (k_render of its share) and everything after it (resolve / pack /
+    # collective / unpack), so that the max-over-ranks step can be attributed
+    mid = frame.phase_events[:a.steps]
+    frame.phase_events = None
+    ph = torch.tensor([sum(k_ev[i][0].elapsed_time(mid[i]) for i in range(a.steps)) / a.steps,
+                       sum(mid[i].elapsed_time(k_ev[i][1]) for i in range(a.steps)) / a.steps], device="cuda")
+    if world > 1:
+        allph = [torch.zeros_like(ph) for _ in range(world)]
+        dist.all_gather(allph, ph)
+    else:
+        allph = [ph]
+    phases = {"render_ms_per_rank": [round(float(x[0]), 3) for x in allph], "exchange_ms_per_rank": [round(float(x[1]), 3) for x in allph]}
 
     # the dominant kernel alone (k_render of this rank's share), events on its launch stream
     kms = []
@@ -244,15 +262,21 @@ def run_b200(a):
     # ---- end to end through the C-ABI with host buffers ------------------------------------
     pinned = torch.empty((a.height, a.width), dtype=torch.int32).pin_memory()
     pinned_np = pinned.numpy().view(np.uint32)
+    # Static texel assets are uploaded once (the reference decodes them once, at start-up: LoadTexture main.cpp:1711-1746);
+    # every timed step re-sends everything else -- geometry, materials, camera -- and rebuilds the BVH.
+    has_tex = any(sc.textures[i].rgba8 for i in range(4))
+    core.upload_scene(sc)
+    sc_step = T.Scene.from_buffer_copy(sc)
+    sc_step.flags |= T.SCENE_KEEP_TEXTURES
     for i in range(2):
-        core.upload_scene(sc)
+        core.upload_scene(sc_step)
         frame.render(a.pp, seed=50 + i)
         if rank == 0:
             core.readback(True, False, out_bgra=pinned_np)
     barrier()
     t0 = time.perf_counter()
     for i in range(a.steps):
-        core.upload_scene(sc)                             # host scene -> device (+ BVH build)
+        core.upload_scene(sc_step)                        # host scene -> device (+ BVH build)
         frame.render(a.pp, seed=1 + i)
         if rank == 0:
             core.readback(True, False, out_bgra=pinned_np)      # device frame -> pinned host memory
@@ -274,12 +298,21 @@ def run_b200(a):
         achieved_tf = algo_flops / (kernel_ms * 1e-3) / 1e12
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         algo_bytes = a.width * a.height * my_share * 20.0
+        rec = ncu_record(a.world, a.width, a.height)
+        executed = None
+        if rec.get("executed_flop_per_sample"):
+            ex_tf = samples_per_step * my_share * rec["executed_flop_per_sample"] / (kernel_ms * 1e-3) / 1e12
+            executed = {"achieved": ex_tf, "unit": "TFLOP/s", "frac": ex_tf / fp32_peak if fp32_peak else None,
+                        "flops_per_sample": rec["executed_flop_per_sample"], "threads_per_inst": rec.get("threads_per_inst"),
+                        "issue_active_pct": rec.get("issue_active_pct"), "warp_inst_per_sample": rec.get("warp_inst_per_sample"),
+                        "source": f"ncu smsp__sass_thread_inst_executed_op_(fadd+fmul+2*ffma) per sample, profiles/k_render_ncu.json, commit {rec.get('commit')}; "
+                                  "x this run's samples / this run's kernel time"}
         roofline = {
             "bound": "fp32", "kernel": "k_render", "achieved": achieved_tf, "peak": fp32_peak, "unit": "TFLOP/s",
-            "frac": achieved_tf / fp32_peak if fp32_peak else None,
+            "frac": achieved_tf / fp32_peak if fp32_peak else None, "executed": executed,
             "peak_source": "measured live: FMA-chain probe pt_measure_fp32_peak (nominal 148 SM x 128 x 2 x 1.965 GHz = 74.4)",
             "flops_per_sample": F_PER_SAMPLE[a.world], "kernel_ms": kernel_ms, "rays_per_sample": rays_per_sample,
-            "traffic": ncu_traffic(a.world),
+            "traffic": rec.get("dram_bytes_per_launch"), "traffic_source": (f"ncu --set full, commit {rec.get('commit')}" if rec else None),
             "hbm": {"bound": "hbm", "achieved": algo_bytes / (kernel_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                     "frac": algo_bytes / (kernel_ms * 1e-3) / 1e9 / hbm_peak,
                     "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s (B200_PROFILING.md)",
@@ -292,9 +325,11 @@ def run_b200(a):
             "config": {"workload": workload_name(a), "world": a.world, "width": a.width, "height": a.height, "pp": a.pp,
                        "shard": a.shard if world > 1 else "none", "rng": "philox4x32-10", "kernel": a.kernel,
                        "l2": "256 MiB memset between timed steps (inside the timed region)"},
-            "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": scene_bytes(sc),
-                    "d2h_bytes_per_step": a.width * a.height * 4},
-            "gpu_launches": launches, "clocks": clocks, "roofline": roofline,
+            "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": scene_bytes(sc, textures=False),
+                    "d2h_bytes_per_step": a.width * a.height * 4,
+                    "textures": (f"{scene_bytes(sc) - scene_bytes(sc, textures=False)} texel bytes uploaded once before the timed region "
+                                 "(PT_SCENE_KEEP_TEXTURES), not per step") if has_tex else "none in this world"},
+            "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "phases": phases,
         }
         if world == 1 and not a.no_cpu_baseline:
             try:

@@ -89,7 +89,11 @@ enum {
     PT_SCENE_NORMAL_MAPS    = 1u << 0,   /* g_bNormals    (cleared by -n, main.cpp:2173) */
     PT_SCENE_METALNESS_MAPS = 1u << 1,   /* g_bMetalness  (cleared by -m, main.cpp:2175) */
     PT_SCENE_ROUGHNESS_MAPS = 1u << 2,   /* g_bRoughness  (cleared by -r, main.cpp:2177) */
-    PT_SCENE_JUST_COSINE    = 1u << 3    /* g_worldKind == WORLD_RAYTRACING_ONE_WEEKEND (main.cpp:654-655) */
+    PT_SCENE_JUST_COSINE    = 1u << 3,   /* g_worldKind == WORLD_RAYTRACING_ONE_WEEKEND (main.cpp:654-655) */
+    /* Upload hint, no reference counterpart (LoadTexture runs once, main.cpp:1711-1746): a texture whose (rgba8 pointer,
+       width, height) equal those of the previous pt_upload_scene on this context has unchanged texels; the device copy is
+       kept and nothing is sent.  Without the flag every upload re-sends every texture. */
+    PT_SCENE_KEEP_TEXTURES  = 1u << 8
 };
 
 /* world_t + camera + textures + flags: everything RenderTexel reads (ray.hpp:152-162) */
@@ -131,6 +135,20 @@ typedef struct pt_config {
     void    *stream;          /* cudaStream_t to launch on; NULL = a stream the context owns */
 } pt_config;
 
+/* Scheduling knobs of the kernels and the BVH builder.  None of them changes a sample: images are bit-identical for
+ * every setting (tests/test_gpu_properties.py); they exist so that a host -- and those tests -- can pin a schedule.
+ * A field left at its "default" value keeps the measured default.  The library reads no environment variable. */
+typedef struct pt_tuning {
+    uint32_t struct_size;        /* = sizeof(pt_tuning) */
+    int32_t  sample_lanes_log2;  /* lanes of a warp that share a pixel = 1 << n, n in 0..5; -1 = default (by launch size) */
+    int32_t  shade_batch;        /* parked lanes before the BRDF code runs, 1..32; 0 = default */
+    int32_t  coop_max;           /* walks entered by <= n lanes are traced by the whole warp, 0..32 (0 = never); -1 = default.
+                                    The cluster cut is built by pt_upload_scene: set this BEFORE uploading the scene. */
+    int32_t  tri_leaf, sph_leaf; /* max primitives per BVH leaf, 1..64; 0 = default (4 / 2).  Applies to the next upload. */
+    int32_t  sah_sweep;          /* 1 = exact sweep for small nodes (default), 0 = 16-bin SAH everywhere; -1 = default */
+    int32_t  wf_pixels_log2;     /* PT_KERNEL_WAVEFRONT: pixels per warp pool; 0 = default */
+} pt_tuning;
+
 enum {
     PT_RENDER_CLEAR = 1u << 0     /* zero the accumulation buffer before rendering */
 };
@@ -161,6 +179,8 @@ typedef struct pt_stats {
     uint32_t kernel_launches; /* kernels launched by the last pt_render */
     uint32_t bvh_nodes;
     uint32_t bvh_prims;
+    uint64_t nan_dropped;     /* samples still NaN after 8 redraws, accumulated as black (the reference would redraw for ever) */
+    uint64_t texture_bytes_uploaded; /* texel bytes the last pt_upload_scene actually sent (0 = all textures were unchanged) */
 } pt_stats;
 
 /* primitive id of a closest hit; kind order = the reference's test order (main.cpp:418-553) */
@@ -187,6 +207,8 @@ int         pt_api_version(void);
 int pt_upload_scene(pt_context *ctx, const pt_scene *scene);
 /* replace only the camera (e.g. a new resolution) without rebuilding the BVH */
 int pt_set_camera(pt_context *ctx, const pt_camera *cam);
+/* scheduling knobs (see pt_tuning); takes effect at the next pt_upload_scene / pt_render */
+int pt_set_tuning(pt_context *ctx, const pt_tuning *tuning);
 
 /* render: asynchronous on the context's stream; pt_readback / pt_synchronize wait for it */
 int pt_render(pt_context *ctx, const pt_render_params *params);
@@ -206,6 +228,17 @@ int pt_set_stream(pt_context *ctx, void *cuda_stream);
 /* pack this rank's tiles (tile-major, 32*32 uint32 each, edge tiles zero-padded) / scatter a packed tile set back */
 int pt_pack_tiles(pt_context *ctx, void *dst_dev, uint32_t tile_rank, uint32_t tile_count, uint32_t *n_tiles_out);
 int pt_unpack_tiles(pt_context *ctx, const void *src_dev, uint32_t tile_rank, uint32_t tile_count);
+/* The same exchange in two kernels per frame instead of resolve + pack + (tile_count - 1) unpacks:
+ *   pt_resolve_pack_tiles : resolve THIS rank's tiles from the accumulator straight into the tile-major pack;
+ *   pt_unpack_gathered    : scatter the packs of all tile_count ranks, gathered back to back with stride_words uint32
+ *                           per rank, into this context's BGRA frame (one thread per pixel) and mark it resolved. */
+int pt_resolve_pack_tiles(pt_context *ctx, void *dst_dev, uint32_t tile_rank, uint32_t tile_count, uint32_t *n_tiles_out);
+int pt_unpack_gathered(pt_context *ctx, const void *src_dev, uint32_t tile_count, uint32_t stride_words);
+/* Sample-range sharding with a reduce-scatter: resolve n_pixels of ANY device accumulator (float4 per pixel: a rank's
+ * share of the reduced sums) into ANY device BGRA buffer; pt_mark_resolved tells the context that its BGRA frame was
+ * filled by the caller (gathered shares), so that pt_readback does not resolve again. */
+int pt_resolve_range(pt_context *ctx, const void *accum_dev, void *bgra_dev, uint32_t n_pixels);
+int pt_mark_resolved(pt_context *ctx);
 
 /* Single-process multi-GPU (one context per device, same frame size): exchange over NVLink peer copies,
  * ordered by events on the two contexts' streams -- the counterpart of the gather / reduce that
@@ -224,10 +257,12 @@ int pt_add_accum_from(pt_context *dst, pt_context *src);
  * word before and after; pathtracer_b200/dist.py, mode "tiles_p2p").  No reference counterpart: the reference's worker
  * threads write their tiles into the one shared g_image (main.cpp:107, 862-866) -- this is that, across GPUs.
  *   pt_frame_ipc_handle : allocate the width x height frame if needed; write the PT_IPC_HANDLE_BYTES blob of its BGRA buffer.
- *                         The handle dies with the frame (a pt_render at another size re-allocates it).
+ *                         An exported frame keeps its size: a later pt_render at another size fails with PT_ERR_INVALID_ARG.
+ *                         Fails with PT_ERR_CUDA when the driver cannot name the frame's allocation (nothing is exported).
  *   pt_open_peer_frame  : map another process's frame; *remote_bgra is a device pointer valid in this process.
- *   pt_resolve_tiles_to : dst_bgra = NULL resolves into the context's own frame. */
-#define PT_IPC_HANDLE_BYTES 72        /* cudaIpcMemHandle_t (64) + the frame's byte offset inside the exported allocation (8) */
+ *   pt_resolve_tiles_to : dst_bgra = NULL resolves into the context's own frame; otherwise dst_bgra must be a frame this
+ *                         context mapped with pt_open_peer_frame, of the same width x height (checked). */
+#define PT_IPC_HANDLE_BYTES 80        /* cudaIpcMemHandle_t (64) + the frame's byte offset inside the exported allocation (8) + width, height (4 + 4) */
 int pt_frame_ipc_handle(pt_context *ctx, int32_t width, int32_t height, void *handle_out);
 int pt_open_peer_frame(pt_context *ctx, const void *handle, void **remote_bgra);
 int pt_close_peer_frame(pt_context *ctx, void *remote_bgra);

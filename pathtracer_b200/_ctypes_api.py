@@ -77,7 +77,15 @@ class Stats(C.Structure):
     _pack_ = 4
     _fields_ = [("samples", C.c_uint64), ("rays", C.c_uint64), ("nan_retries", C.c_uint64),
                 ("render_ms", C.c_float), ("kernel_launches", C.c_uint32),
-                ("bvh_nodes", C.c_uint32), ("bvh_prims", C.c_uint32)]
+                ("bvh_nodes", C.c_uint32), ("bvh_prims", C.c_uint32),
+                ("nan_dropped", C.c_uint64), ("texture_bytes_uploaded", C.c_uint64)]
+
+
+class Tuning(C.Structure):
+    _pack_ = 4
+    _fields_ = [("struct_size", C.c_uint32), ("sample_lanes_log2", C.c_int32), ("shade_batch", C.c_int32),
+                ("coop_max", C.c_int32), ("tri_leaf", C.c_int32), ("sph_leaf", C.c_int32), ("sah_sweep", C.c_int32),
+                ("wf_pixels_log2", C.c_int32)]
 
 
 class HostOptions(C.Structure):
@@ -114,6 +122,7 @@ assert HIT_DTYPE.itemsize == 28
 
 SCENE_NORMAL_MAPS, SCENE_METALNESS_MAPS, SCENE_ROUGHNESS_MAPS, SCENE_JUST_COSINE = 1, 2, 4, 8
 SCENE_ALL_MAPS = 7
+SCENE_KEEP_TEXTURES = 1 << 8
 RENDER_CLEAR = 1
 BVH_HOST_SAH, BVH_DEVICE_LBVH = 0, 1
 KERNEL_AUTO, KERNEL_MEGA, KERNEL_WAVEFRONT = 0, 1, 2

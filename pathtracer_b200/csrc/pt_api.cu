@@ -32,7 +32,16 @@ struct pt_context {
     cudaStream_t stream = nullptr;
     bool own_stream = false;
     std::string error;
-    std::vector<void *> scene_allocs;          // freed on re-upload / destroy
+    // Scene storage.  All the small arrays of a scene (nodes, records, materials, index tables) are laid out in ONE pinned
+    // host staging buffer and copied with ONE cudaMemcpyAsync into a device arena of the same layout; both persist across
+    // uploads and only grow.  Textures keep their own device buffers, reused while (width, height) is unchanged.
+    char *arena_host = nullptr, *arena_dev = nullptr;
+    size_t arena_cap = 0, arena_used = 0;
+    std::vector<std::pair<size_t, std::vector<char>>> arena_overflow;   // (offset, bytes) written past arena_cap during a layout pass
+    struct TexSlot { void *dev = nullptr; size_t bytes = 0; int w = 0, h = 0; const void *host = nullptr; };
+    TexSlot tex_slots[4];
+    uint64_t tex_bytes_uploaded = 0;
+    bool frame_exported = false;               // pt_frame_ipc_handle handed this frame to peers: it must not be re-allocated
     PtDeviceScene scene{};
     bool has_scene = false;
     uint32_t features = PT_F_ALL;              // PT_F_* of the uploaded scene -> k_render variant
@@ -48,21 +57,22 @@ struct pt_context {
     uint32_t last_launches = 0;
     uint32_t bvh_nodes = 0, bvh_prims = 0;
     PtWavefront wf;
+    // scheduling knobs (pt_set_tuning); none of them changes a sample's value
     int sample_lanes_log2 = -1;                // -1 = auto
-    bool sah_sweep = true;                     // PT_SAH_SWEEP=0: 16-bin SAH everywhere (experiment)
-    int tri_leaf = 4, sph_leaf = 2;            // max primitives per BVH leaf (PT_TRI_LEAF / PT_SPH_LEAF; measured, profiles/r01f)
-    int shade_batch = 0;                       // PT_SHADE_BATCH: deferral threshold of k_render (0 = per-variant default)
+    bool sah_sweep = true;                     // false: 16-bin SAH everywhere
+    int tri_leaf = 4, sph_leaf = 2;            // max primitives per BVH leaf (measured, profiles/r01f)
+    int shade_batch = 0;                       // deferral threshold of k_render (0 = per-variant default)
     // Walks entered by <= coop_max lanes of a warp are traced cooperatively (k_render<... | PT_F_COOP>).  -1 = the measured
     // default: 12 for a triangle tree (w5 +8.4 %), off for a sphere tree (w2 -0.5 %, w4 +0.6 %; profiles/r01h_coop_check.jsonl).
-    // PT_COOP_MAX=n overrides it for both kinds of tree (0 = off).
+    // pt_tuning.coop_max = n overrides it for both kinds of tree (0 = off).
     int coop_max = -1;
-    int min_trace = 1;                         // PT_SHADE_MIN_TRACE, read by -DPT_X_SHADE_RULE builds only
     // single-process multi-GPU (pt_gather_tiles_from / pt_add_accum_from)
     void *pack_buf = nullptr, *stage_buf = nullptr;
     size_t pack_bytes = 0, stage_bytes = 0;
     cudaEvent_t ev_sent = nullptr, ev_stage_free = nullptr;
     bool stage_in_use = false;
-    std::vector<std::pair<void *, void *>> peer_maps;   // pt_open_peer_frame: (frame pointer, base of the mapped allocation)
+    struct PeerMap { void *frame, *base; int w, h; };
+    std::vector<PeerMap> peer_maps;            // pt_open_peer_frame: frame pointer, base of the mapped allocation, the frame's size
     void *flush_buf = nullptr;                 // pt_flush_l2
     size_t flush_bytes = 0;
     int flush_value = 0;
@@ -92,6 +102,7 @@ extern "C" int pt_destroy(pt_context *ctx);
 extern "C" int pt_create(const pt_config *cfg, pt_context **out) {
     if (!out) return fail(nullptr, PT_ERR_INVALID_ARG, "pt_create: out is NULL");
     *out = nullptr;
+    if (cfg && cfg->struct_size != sizeof(pt_config)) return fail(nullptr, PT_ERR_INVALID_ARG, "pt_create: struct_size mismatch");
     int n = 0;
     cudaError_t e = cudaGetDeviceCount(&n);
     if (e != cudaSuccess || n == 0)
@@ -125,25 +136,25 @@ extern "C" int pt_create(const pt_config *cfg, pt_context **out) {
         return fail(nullptr, PT_ERR_OOM, "cudaMalloc failed");
     }
     cudaMemset(ctx->counters, 0, PT_N_COUNTERS * sizeof(unsigned long long));
+#ifdef PT_DEBUG_ENV      // debug builds only (make -C pathtracer_b200/csrc debug): sweeps from the shell; the product reads no environment
     if (const char *s = getenv("PT_SAMPLE_LANES_LOG2")) ctx->sample_lanes_log2 = atoi(s);
     if (const char *s = getenv("PT_SHADE_BATCH")) ctx->shade_batch = atoi(s);
     if (const char *s = getenv("PT_COOP_MAX")) ctx->coop_max = std::max(0, std::min(32, atoi(s)));
-    if (const char *s = getenv("PT_SHADE_MIN_TRACE")) ctx->min_trace = std::max(1, std::min(33, atoi(s)));
     if (const char *s = getenv("PT_SAH_SWEEP")) ctx->sah_sweep = atoi(s) != 0;
     if (const char *s = getenv("PT_TRI_LEAF")) ctx->tri_leaf = std::max(1, std::min(64, atoi(s)));
     if (const char *s = getenv("PT_SPH_LEAF")) ctx->sph_leaf = std::max(1, std::min(64, atoi(s)));
     if (const char *s = getenv("PT_WF_PIXELS_LOG2")) ctx->wf.pixels_log2 = atoi(s);
-    if (const char *s = getenv("PT_KERNEL")) {          // experiments: overrides pt_config.kernel
-        if (!strcmp(s, "mega")) ctx->kernel = PT_KERNEL_MEGA;
-        else if (!strcmp(s, "wavefront")) ctx->kernel = PT_KERNEL_WAVEFRONT;
-    }
+#endif
     *out = ctx;
     return PT_OK;
 }
 
 static void free_scene(pt_context *ctx) {
-    for (void *p : ctx->scene_allocs) cudaFree(p);
-    ctx->scene_allocs.clear();
+    if (ctx->arena_host) cudaFreeHost(ctx->arena_host);
+    if (ctx->arena_dev) cudaFree(ctx->arena_dev);
+    ctx->arena_host = ctx->arena_dev = nullptr;
+    ctx->arena_cap = ctx->arena_used = 0;
+    for (auto &t : ctx->tex_slots) { if (t.dev) cudaFree(t.dev); t = pt_context::TexSlot(); }
     ctx->has_scene = false;
 }
 
@@ -161,7 +172,7 @@ extern "C" int pt_destroy(pt_context *ctx) {
     free_scene(ctx);
     free_frame(ctx);
     ctx->wf.release();
-    for (auto &m : ctx->peer_maps) cudaIpcCloseMemHandle(m.second);
+    for (auto &m : ctx->peer_maps) cudaIpcCloseMemHandle(m.base);
     ctx->peer_maps.clear();
     if (ctx->counters) cudaFree(ctx->counters);
     if (ctx->pack_buf) cudaFree(ctx->pack_buf);
@@ -185,16 +196,44 @@ extern "C" int pt_set_stream(pt_context *ctx, void *s) {
     return PT_OK;
 }
 
+// Bump allocation of one scene array in the arena (256-byte aligned).  Bytes that do not fit are parked in
+// arena_overflow; arena_commit() then grows both buffers and replays them, so a scene is laid out in one pass.
+static size_t arena_put(pt_context *ctx, const void *src, size_t bytes) {
+    const size_t off = (ctx->arena_used + 255) & ~(size_t)255;
+    ctx->arena_used = off + bytes;
+    if (ctx->arena_used <= ctx->arena_cap) memcpy(ctx->arena_host + off, src, bytes);
+    else ctx->arena_overflow.emplace_back(off, std::vector<char>((const char *)src, (const char *)src + bytes));
+    return off;
+}
+
+// Device pointers handed out by upload() are OFFSETS until arena_commit() rebases them (the arena may have to grow).
 template <typename T>
 static int upload(pt_context *ctx, const std::vector<T> &v, const T **out) {
     *out = nullptr;
     if (v.empty()) return PT_OK;
-    void *p = nullptr;
-    CK(cudaMalloc(&p, v.size() * sizeof(T)));
-    ctx->scene_allocs.push_back(p);
-    CK(cudaMemcpyAsync(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
-    *out = (const T *)p;
+    *out = reinterpret_cast<const T *>(arena_put(ctx, v.data(), v.size() * sizeof(T)) + 1);      // +1: offset 0 stays distinct from NULL
     return PT_OK;
+}
+
+static int arena_commit(pt_context *ctx) {
+    if (ctx->arena_used > ctx->arena_cap) {
+        size_t cap = ctx->arena_cap ? ctx->arena_cap : (size_t)1 << 20;
+        while (cap < ctx->arena_used) cap *= 2;
+        char *h = nullptr, *d = nullptr;
+        CK(cudaMallocHost((void **)&h, cap));
+        if (cudaMalloc((void **)&d, cap) != cudaSuccess) { cudaFreeHost(h); cudaGetLastError(); return fail(ctx, PT_ERR_OOM, "pt_upload_scene: cudaMalloc failed"); }
+        if (ctx->arena_host) { memcpy(h, ctx->arena_host, std::min(ctx->arena_cap, ctx->arena_used)); cudaFreeHost(ctx->arena_host); }
+        if (ctx->arena_dev) cudaFree(ctx->arena_dev);
+        ctx->arena_host = h; ctx->arena_dev = d; ctx->arena_cap = cap;
+    }
+    for (auto &o : ctx->arena_overflow) memcpy(ctx->arena_host + o.first, o.second.data(), o.second.size());
+    ctx->arena_overflow.clear();
+    if (ctx->arena_used) CK(cudaMemcpyAsync(ctx->arena_dev, ctx->arena_host, ctx->arena_used, cudaMemcpyHostToDevice, ctx->stream));
+    return PT_OK;
+}
+template <typename T>
+static void rebase(const pt_context *ctx, const T *&p) {
+    if (p) p = reinterpret_cast<const T *>(ctx->arena_dev + (reinterpret_cast<uintptr_t>(p) - 1));
 }
 
 static inline void v3sub(const float *a, const float *b, float *r) { r[0] = a[0] - b[0]; r[1] = a[1] - b[1]; r[2] = a[2] - b[2]; }
@@ -287,8 +326,10 @@ extern "C" int pt_upload_scene(pt_context *ctx, const pt_scene *s) {
         return fail(ctx, PT_ERR_INVALID_ARG, "pt_upload_scene: a primitive count is non-zero but its array is NULL");
     if (s->n_triangles >= (1u << 24)) return fail(ctx, PT_ERR_UNSUPPORTED, "pt_upload_scene: more than 2^24 - 1 triangles (leaf links hold 24-bit positions)");
     CK(cudaSetDevice(ctx->device));
-    CK(cudaStreamSynchronize(ctx->stream));
-    free_scene(ctx);
+    CK(cudaStreamSynchronize(ctx->stream));          // the previous scene may still be read, and the staging buffer copied
+    ctx->has_scene = false;
+    ctx->arena_used = 0;
+    ctx->arena_overflow.clear();
     PtDeviceScene D{};
     int rc;
 
@@ -412,15 +453,28 @@ extern "C" int pt_upload_scene(pt_context *ctx, const pt_scene *s) {
         for (int i = 0; i < 256; i++) lut[i] = (float)i / 255.f;          // IEEE division, as LoadTexture does per texel
         if ((rc = upload(ctx, lut, &d_unit255))) return rc;
     }
+    // Texels: one persistent device buffer per slot, re-allocated only when the size changes.  With PT_SCENE_KEEP_TEXTURES
+    // the host vouches that a texture whose (pointer, width, height) equal the previous upload's is unchanged: nothing is
+    // sent (a host that moves the camera or the geometry does not re-send 64 MB of texels every frame).
+    ctx->tex_bytes_uploaded = 0;
     for (int i = 0; i < 4; i++) {
         const pt_texture &t = s->textures[i];
-        if (!t.rgba8 || t.width <= 0 || t.height <= 0) continue;
-        void *p = nullptr;
-        size_t bytes = (size_t)t.width * t.height * 4;
-        CK(cudaMalloc(&p, bytes));
-        ctx->scene_allocs.push_back(p);
-        CK(cudaMemcpyAsync(p, t.rgba8, bytes, cudaMemcpyHostToDevice, ctx->stream));
-        D.tex[i].texels = (const uchar4 *)p;
+        pt_context::TexSlot &slot = ctx->tex_slots[i];
+        if (!t.rgba8 || t.width <= 0 || t.height <= 0) { slot.host = nullptr; slot.w = slot.h = 0; continue; }
+        const size_t bytes = (size_t)t.width * t.height * 4;
+        const bool keep = (s->flags & PT_SCENE_KEEP_TEXTURES) && slot.dev && slot.host == t.rgba8 && slot.w == t.width && slot.h == t.height;
+        if (!keep) {
+            if (slot.bytes != bytes) {
+                if (slot.dev) cudaFree(slot.dev);
+                slot = pt_context::TexSlot();
+                CK(cudaMalloc(&slot.dev, bytes));
+                slot.bytes = bytes;
+            }
+            CK(cudaMemcpyAsync(slot.dev, t.rgba8, bytes, cudaMemcpyHostToDevice, ctx->stream));
+            slot.host = t.rgba8; slot.w = t.width; slot.h = t.height;
+            ctx->tex_bytes_uploaded += bytes;
+        }
+        D.tex[i].texels = (const uchar4 *)slot.dev;
         D.tex[i].w = t.width; D.tex[i].h = t.height;
         D.tex[i].unit255 = d_unit255;
         D.tex[i].wmask = (t.width > 1 && (t.width & (t.width - 1)) == 0) ? t.width - 1 : 0;
@@ -433,12 +487,36 @@ extern "C" int pt_upload_scene(pt_context *ctx, const pt_scene *s) {
             if (idx[k] < 0 || idx[k] > 4 || (idx[k] > 0 && !D.tex[idx[k] - 1].texels))
                 return fail(ctx, PT_ERR_INVALID_ARG, "material references a texture that was not supplied");
     }
-    D.flags = s->flags;
+    D.flags = s->flags & ~(uint32_t)PT_SCENE_KEEP_TEXTURES;
     D.cam = s->camera;
-    CK(cudaStreamSynchronize(ctx->stream));     // the host vectors above go out of scope
+    // one H2D copy of the whole arena (asynchronous: the staging buffer is pinned and persists), then offsets -> pointers
+    if ((rc = arena_commit(ctx))) return rc;
+    rebase(ctx, D.lin_spheres); rebase(ctx, D.lin_sphere_ids); rebase(ctx, D.planes); rebase(ctx, D.quads); rebase(ctx, D.aabbs);
+    rebase(ctx, D.sphere_bvh.nodes); rebase(ctx, D.bvh_spheres); rebase(ctx, D.bvh_sphere_ids);
+    rebase(ctx, D.tri_bvh.nodes); rebase(ctx, D.tris); rebase(ctx, D.tri_ids); rebase(ctx, D.tri_normals);
+    rebase(ctx, D.materials); rebase(ctx, D.sphere_mat); rebase(ctx, D.plane_mat); rebase(ctx, D.quad_mat); rebase(ctx, D.aabb_mat); rebase(ctx, D.tri_mat);
+    rebase(ctx, D.all_spheres); rebase(ctx, D.tri_clusters); rebase(ctx, D.sph_clusters);
+    for (int i = 0; i < 4; i++) rebase(ctx, D.tex[i].unit255);
     ctx->scene = D;
     ctx->features = scene_features(D, s);
     ctx->has_scene = true;
+    return PT_OK;
+}
+
+extern "C" int pt_set_tuning(pt_context *ctx, const pt_tuning *t) {
+    if (!ctx || !t) return PT_ERR_INVALID_ARG;
+    if (t->struct_size != sizeof(pt_tuning)) return fail(ctx, PT_ERR_INVALID_ARG, "pt_set_tuning: struct_size mismatch");
+    if (t->sample_lanes_log2 < -1 || t->sample_lanes_log2 > 5 || t->shade_batch < 0 || t->shade_batch > 32 || t->coop_max < -1 || t->coop_max > 32 ||
+        t->tri_leaf < 0 || t->tri_leaf > 64 || t->sph_leaf < 0 || t->sph_leaf > 64 || t->sah_sweep < -1 || t->sah_sweep > 1 ||
+        t->wf_pixels_log2 < 0 || t->wf_pixels_log2 > 10)
+        return fail(ctx, PT_ERR_INVALID_ARG, "pt_set_tuning: a field is out of range");
+    ctx->sample_lanes_log2 = t->sample_lanes_log2;
+    ctx->shade_batch = t->shade_batch;
+    ctx->coop_max = t->coop_max;
+    ctx->tri_leaf = t->tri_leaf ? t->tri_leaf : 4;
+    ctx->sph_leaf = t->sph_leaf ? t->sph_leaf : 2;
+    ctx->sah_sweep = t->sah_sweep != 0;
+    if (t->wf_pixels_log2) ctx->wf.pixels_log2 = t->wf_pixels_log2;
     return PT_OK;
 }
 
@@ -453,8 +531,13 @@ extern "C" int pt_set_camera(pt_context *ctx, const pt_camera *cam) {
 // ------------------------------------------------------------------------------------------------
 static int ensure_frame(pt_context *ctx, int w, int h) {
     if (ctx->width == w && ctx->height == h && ctx->accum) return PT_OK;
+    if ((uint64_t)w * (uint64_t)h > 0x7fffffffull) return fail(ctx, PT_ERR_UNSUPPORTED, "frame larger than 2^31 - 1 pixels");
+    if (ctx->frame_exported)
+        return fail(ctx, PT_ERR_INVALID_ARG, "the frame was exported with pt_frame_ipc_handle and peers may still map it: "
+                                             "it cannot change size (destroy the context, or keep rendering at the exported size)");
     CK(cudaStreamSynchronize(ctx->stream));
     free_frame(ctx);
+    CK(cudaMemsetAsync(ctx->counters, 0, PT_N_COUNTERS * sizeof(unsigned long long), ctx->stream));      // statistics never span frames
     size_t n = (size_t)w * h;
     CK(cudaMalloc((void **)&ctx->accum, n * sizeof(float4)));
     CK(cudaMalloc((void **)&ctx->bgra, n * sizeof(uint32_t)));
@@ -499,10 +582,6 @@ extern "C" int pt_render(pt_context *ctx, const pt_render_params *p) {
     A.tiles_y = (uint32_t)(p->height + PT_TILE - 1) / PT_TILE;
     A.n_my_tiles = my_tile_count(A.tiles_x * A.tiles_y, p->tile_rank, tile_count);
     A.seed = p->seed;
-    for (uint32_t r = 0; r < 10; r++) {
-        A.philox_k[2 * r] = (uint32_t)p->seed + r * 0x9E3779B9u;
-        A.philox_k[2 * r + 1] = (uint32_t)(p->seed >> 32) + r * 0xBB67AE85u;
-    }
     A.accum = ctx->accum;
     A.counters = ctx->counters;
 
@@ -527,7 +606,6 @@ extern "C" int pt_render(pt_context *ctx, const pt_render_params *p) {
             A.log2_sample_lanes = lS;
             // parked lanes before the BRDF code runs (variants with PT_F_DEFER): measured best 32 with textures, else 20
             A.shade_batch = ctx->shade_batch > 0 ? (uint32_t)ctx->shade_batch : ((ctx->features & PT_F_TEX) ? 32u : 20u);
-            A.min_trace = (uint32_t)ctx->min_trace;
             // cooperative sparse walks only where exactly one tree exists and it has a cluster cut
             const bool one_tree = (ctx->scene.tri_bvh.n_nodes != 0) != (ctx->scene.sphere_bvh.n_nodes != 0);
             const bool has_cut = ctx->scene.tri_bvh.n_nodes ? ctx->scene.n_tri_clusters != 0 : ctx->scene.n_sph_clusters != 0;
@@ -536,7 +614,8 @@ extern "C" int pt_render(pt_context *ctx, const pt_render_params *p) {
             uint64_t warps = (uint64_t)A.n_my_tiles * warps_per_tile;
             const uint32_t wpb = PT_RENDER_THREADS / 32;
             uint64_t blocks = (warps + wpb - 1) / wpb;
-            if (blocks > 0x7fffffffull) return fail(ctx, PT_ERR_UNSUPPORTED, "pt_render: frame too large for one launch");
+            // k_render derives its warp index from blockIdx.x * blockDim.x in 32 bits
+            if (blocks > 0xffffffffull / PT_RENDER_THREADS - 1) return fail(ctx, PT_ERR_UNSUPPORTED, "pt_render: frame too large for one launch");
             launch_render(ctx->features, (unsigned)blocks, ctx->stream, ctx->scene, A);
             ctx->last_launches = 1;
         }
@@ -586,18 +665,6 @@ extern "C" int pt_readback(pt_context *ctx, uint32_t *bgra, float *accum_rgba, p
     if (accum_rgba) CK(cudaMemcpyAsync(accum_rgba, ctx->accum, n * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
     unsigned long long c[4] = {0, 0, 0, 0};
     if (stats) CK(cudaMemcpyAsync(c, ctx->counters, sizeof(c), cudaMemcpyDeviceToHost, ctx->stream));
-#ifdef PT_STATS_HIST
-    if (stats) {      // experiment build: BVH-walk occupancy histogram (tools/README)
-        unsigned long long hc[PT_N_COUNTERS];
-        CK(cudaMemcpyAsync(hc, ctx->counters, sizeof(hc), cudaMemcpyDeviceToHost, ctx->stream));
-        CK(cudaStreamSynchronize(ctx->stream));
-        unsigned long long walks = 0, steps = 0;
-        for (int k = 1; k <= 32; k++) { walks += hc[4 + k]; steps += hc[4 + 33 + k]; }
-        fprintf(stderr, "[pt_stats] lanes-at-entry : share of walk launches : share of node steps (thread-level)\n");
-        for (int k = 1; k <= 32; k++)
-            fprintf(stderr, "[pt_stats] %2d : %6.2f%% : %6.2f%%\n", k, 100.0 * hc[4 + k] / (double)(walks ? walks : 1), 100.0 * hc[4 + 33 + k] / (double)(steps ? steps : 1));
-    }
-#endif
     CK(cudaStreamSynchronize(ctx->stream));
     if (stats) {
         memset(stats, 0, sizeof(*stats));
@@ -608,6 +675,8 @@ extern "C" int pt_readback(pt_context *ctx, uint32_t *bgra, float *accum_rgba, p
         stats->kernel_launches = ctx->last_launches;
         stats->bvh_nodes = ctx->bvh_nodes;
         stats->bvh_prims = ctx->bvh_prims;
+        stats->nan_dropped = c[2];
+        stats->texture_bytes_uploaded = ctx->tex_bytes_uploaded;
     }
     return PT_OK;
 }
@@ -645,32 +714,84 @@ extern "C" int pt_unpack_tiles(pt_context *ctx, const void *src, uint32_t rank, 
     return PT_OK;
 }
 
+extern "C" int pt_resolve_pack_tiles(pt_context *ctx, void *dst, uint32_t rank, uint32_t count, uint32_t *n_out) {
+    if (!ctx || !dst || count == 0 || rank >= count) return PT_ERR_INVALID_ARG;
+    if (!ctx->accum) return fail(ctx, PT_ERR_NO_FRAME, "pt_resolve_pack_tiles: nothing rendered yet");
+    CK(cudaSetDevice(ctx->device));
+    uint32_t tiles_x = (uint32_t)(ctx->width + PT_TILE - 1) / PT_TILE, tiles_y = (uint32_t)(ctx->height + PT_TILE - 1) / PT_TILE;
+    uint32_t n = my_tile_count(tiles_x * tiles_y, rank, count);
+    if (n_out) *n_out = n;
+    if (n) k_resolve_pack_tiles<<<(n * 1024u + 255u) / 256u, 256, 0, ctx->stream>>>(ctx->accum, (uint32_t *)dst, ctx->width, ctx->height, tiles_x, rank, count, n);
+    CK(cudaGetLastError());
+    return PT_OK;
+}
+
+extern "C" int pt_unpack_gathered(pt_context *ctx, const void *src, uint32_t count, uint32_t stride_words) {
+    if (!ctx || !src || count == 0) return PT_ERR_INVALID_ARG;
+    if (!ctx->bgra) return fail(ctx, PT_ERR_NO_FRAME, "pt_unpack_gathered: no frame");
+    CK(cudaSetDevice(ctx->device));
+    uint32_t tiles_x = (uint32_t)(ctx->width + PT_TILE - 1) / PT_TILE, tiles_y = (uint32_t)(ctx->height + PT_TILE - 1) / PT_TILE;
+    if (stride_words < my_tile_count(tiles_x * tiles_y, 0, count) * 1024u) return fail(ctx, PT_ERR_INVALID_ARG, "pt_unpack_gathered: stride shorter than rank 0's pack");
+    uint32_t n = (uint32_t)ctx->width * (uint32_t)ctx->height;
+    k_unpack_gathered<<<(n + 255u) / 256u, 256, 0, ctx->stream>>>(ctx->bgra, (const uint32_t *)src, ctx->width, ctx->height, tiles_x, count, stride_words);
+    CK(cudaGetLastError());
+    ctx->resolved = true;          // the frame now holds every rank's resolved tiles
+    return PT_OK;
+}
+
+extern "C" int pt_resolve_range(pt_context *ctx, const void *accum_dev, void *bgra_dev, uint32_t n_pixels) {
+    if (!ctx || !accum_dev || !bgra_dev) return PT_ERR_INVALID_ARG;
+    if (n_pixels == 0) return PT_OK;
+    CK(cudaSetDevice(ctx->device));
+    k_resolve_range<<<(n_pixels + 255u) / 256u, 256, 0, ctx->stream>>>((const float4 *)accum_dev, (uint32_t *)bgra_dev, n_pixels);
+    CK(cudaGetLastError());
+    return PT_OK;
+}
+
+extern "C" int pt_mark_resolved(pt_context *ctx) {
+    if (!ctx) return PT_ERR_INVALID_ARG;
+    if (!ctx->bgra) return fail(ctx, PT_ERR_NO_FRAME, "pt_mark_resolved: no frame");
+    ctx->resolved = true;
+    return PT_OK;
+}
+
 // ---- one process per GPU: tiles resolved straight into the root rank's frame over NVLink peer memory ----------
 // An IPC handle names the whole driver allocation a pointer lives in (small cudaMallocs are carved out of shared slabs), and
 // opening it yields that allocation's base: the blob handed to the peers is therefore handle + offset of the frame in it.
 // cuMemGetAddressRange comes through the runtime's entry-point query, so the library does not link against libcuda.
-static size_t offset_in_allocation(const void *p) {
+static bool offset_in_allocation(const void *p, uint64_t *off) {
     void *fn = nullptr;
     cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuMemGetAddressRange", &fn, cudaEnableDefault, &q) != cudaSuccess || !fn) { cudaGetLastError(); return 0; }
+    if (cudaGetDriverEntryPoint("cuMemGetAddressRange", &fn, cudaEnableDefault, &q) != cudaSuccess || !fn) { cudaGetLastError(); return false; }
     typedef int (*range_fn)(unsigned long long *, size_t *, unsigned long long);
     unsigned long long base = 0;
     size_t size = 0;
-    if (((range_fn)fn)(&base, &size, (unsigned long long)(uintptr_t)p) != 0 || base == 0) return 0;
-    return (size_t)((unsigned long long)(uintptr_t)p - base);
+    if (((range_fn)fn)(&base, &size, (unsigned long long)(uintptr_t)p) != 0 || base == 0) return false;
+    *off = (unsigned long long)(uintptr_t)p - base;
+    return true;
 }
 
+// the blob: cudaIpcMemHandle_t (64 bytes) | byte offset of the frame in the exported allocation (8) | width (4) | height (4)
+struct PtIpcBlob {
+    cudaIpcMemHandle_t handle;
+    uint64_t offset;
+    int32_t width, height;
+};
+
 extern "C" int pt_frame_ipc_handle(pt_context *ctx, int32_t width, int32_t height, void *handle_out) {
-    static_assert(sizeof(cudaIpcMemHandle_t) + sizeof(uint64_t) == PT_IPC_HANDLE_BYTES, "PT_IPC_HANDLE_BYTES = cudaIpcMemHandle_t + offset");
+    static_assert(sizeof(PtIpcBlob) == PT_IPC_HANDLE_BYTES, "PT_IPC_HANDLE_BYTES = cudaIpcMemHandle_t + offset + width + height");
     if (!ctx || !handle_out || width <= 0 || height <= 0) return PT_ERR_INVALID_ARG;
     CK(cudaSetDevice(ctx->device));
     int rc = ensure_frame(ctx, width, height);
     if (rc) return rc;
-    cudaIpcMemHandle_t h;
-    CK(cudaIpcGetMemHandle(&h, ctx->bgra));
-    const uint64_t off = (uint64_t)offset_in_allocation(ctx->bgra);
-    memcpy(handle_out, &h, sizeof(h));
-    memcpy((char *)handle_out + sizeof(h), &off, sizeof(off));
+    PtIpcBlob b;
+    memset(&b, 0, sizeof(b));
+    CK(cudaIpcGetMemHandle(&b.handle, ctx->bgra));
+    if (!offset_in_allocation(ctx->bgra, &b.offset))
+        return fail(ctx, PT_ERR_CUDA, "pt_frame_ipc_handle: cuMemGetAddressRange is unavailable or failed; the frame cannot be exported");
+    b.width = width; b.height = height;
+    memcpy(handle_out, &b, sizeof(b));
+    ctx->frame_exported = true;
     return PT_OK;
 }
 
@@ -678,14 +799,13 @@ extern "C" int pt_open_peer_frame(pt_context *ctx, const void *handle, void **re
     if (!ctx || !handle || !remote_bgra) return PT_ERR_INVALID_ARG;
     *remote_bgra = nullptr;
     CK(cudaSetDevice(ctx->device));
-    cudaIpcMemHandle_t h;
-    uint64_t off = 0;
-    memcpy(&h, handle, sizeof(h));
-    memcpy(&off, (const char *)handle + sizeof(h), sizeof(off));
+    PtIpcBlob b;
+    memcpy(&b, handle, sizeof(b));
+    if (b.width <= 0 || b.height <= 0) return fail(ctx, PT_ERR_INVALID_ARG, "pt_open_peer_frame: not a frame handle");
     void *base = nullptr;
-    CK(cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess));
-    void *p = (char *)base + off;
-    ctx->peer_maps.push_back({p, base});
+    CK(cudaIpcOpenMemHandle(&base, b.handle, cudaIpcMemLazyEnablePeerAccess));
+    void *p = (char *)base + b.offset;
+    ctx->peer_maps.push_back({p, base, b.width, b.height});
     *remote_bgra = p;
     return PT_OK;
 }
@@ -696,8 +816,8 @@ extern "C" int pt_close_peer_frame(pt_context *ctx, void *remote_bgra) {
     CK(cudaSetDevice(ctx->device));
     CK(cudaStreamSynchronize(ctx->stream));
     for (size_t i = 0; i < ctx->peer_maps.size(); i++)
-        if (ctx->peer_maps[i].first == remote_bgra) {
-            void *base = ctx->peer_maps[i].second;
+        if (ctx->peer_maps[i].frame == remote_bgra) {
+            void *base = ctx->peer_maps[i].base;
             ctx->peer_maps.erase(ctx->peer_maps.begin() + i);
             CK(cudaIpcCloseMemHandle(base));
             return PT_OK;
@@ -712,6 +832,11 @@ extern "C" int pt_resolve_tiles_to(pt_context *ctx, void *dst_bgra, uint32_t ran
     uint32_t tiles_x = (uint32_t)(ctx->width + PT_TILE - 1) / PT_TILE, tiles_y = (uint32_t)(ctx->height + PT_TILE - 1) / PT_TILE;
     uint32_t n = my_tile_count(tiles_x * tiles_y, rank, count);
     uint32_t *dst = dst_bgra ? (uint32_t *)dst_bgra : ctx->bgra;
+    if (dst_bgra) {          // a destination other than the own frame must be a mapped peer frame of exactly this size
+        bool ok = false;
+        for (auto &m : ctx->peer_maps) ok = ok || (m.frame == dst_bgra && m.w == ctx->width && m.h == ctx->height);
+        if (!ok) return fail(ctx, PT_ERR_INVALID_ARG, "pt_resolve_tiles_to: dst is not a peer frame mapped by this context with the same width x height");
+    }
     if (n) k_resolve_tiles_to<<<(n * 1024u + 255u) / 256u, 256, 0, ctx->stream>>>(ctx->accum, dst, ctx->width, ctx->height, tiles_x, rank, count, n);
     CK(cudaGetLastError());
     if (!dst_bgra) ctx->resolved = true;       // own frame: the caller vouches that peers fill the other ranks' tiles (pt_readback must not re-resolve)

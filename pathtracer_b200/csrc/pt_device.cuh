@@ -168,39 +168,14 @@ __device__ __forceinline__ float u32_to_unit(uint32_t x) {
 
 // One Philox block (4 uniforms) per path vertex: the camera uses block 0 (words 0,1), and every iteration of
 // RayCast's sampling loop (main.cpp:660) starts on the next block -- coin, [coin, r1, r2] or [z1, z2].
-#ifdef PT_X_PHILOX_KEYS
-// Experiment build (tools/r02_experiments.sh): the ten round keys (k0 + r*0x9E3779B9, k1 + r*0xBB67AE85) depend on the render
-// seed only, so pt_render computes them once into the kernel parameters and the rounds read them from the constant bank --
-// the 20 UIADD3 per block (a third of Philox's instructions: uniform-datapath ops still take issue slots) disappear, and
-// the two key registers with them.  Same keys, same words.
-__device__ __forceinline__ uint4 philox4x32_10k(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, const uint32_t *__restrict__ K) {
-#pragma unroll
-    for (int r = 0; r < 10; r++) {
-        uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
-        uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
-        c0 = hi1 ^ c1 ^ K[2 * r];
-        c1 = lo1;
-        c2 = hi0 ^ c3 ^ K[2 * r + 1];
-        c3 = lo0;
-    }
-    return make_uint4(c0, c1, c2, c3);
-}
-#endif
-
 struct PtRng {
     uint32_t k0, k1, a, b, tag, blk;
-#ifdef PT_X_PHILOX_KEYS
-    const uint32_t *K = nullptr;      // precomputed round keys (k_render: PtRenderArgs::philox_k); null = derive them from k0, k1
-#endif
     __device__ __forceinline__ void init(uint64_t seed, uint32_t a_, uint32_t b_, uint32_t tag_) {
         k0 = (uint32_t)seed; k1 = (uint32_t)(seed >> 32);
         a = a_; b = b_; tag = tag_; blk = 0;
     }
     // one block of an arbitrary stream of the same seed (the thin-lens film stream)
     __device__ __forceinline__ uint4 block_of(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3) const {
-#ifdef PT_X_PHILOX_KEYS
-        if (K) return philox4x32_10k(c0, c1, c2, c3, K);
-#endif
         return philox4x32_10(c0, c1, c2, c3, k0, k1);
     }
     __device__ __forceinline__ uint4 next_block() {
@@ -221,7 +196,6 @@ enum : uint32_t {
     PT_F_LIGHT = 32u,     // importance-sample spheres[0] (everything but PT_SCENE_JUST_COSINE)
     PT_F_ALL = 63u | 128u,
     PT_F_DEFER = 64u,     // kernel policy, not a scene feature: park lanes that need a BRDF sample (pt_kernels.cuh)
-    PT_F_QUEUE = 256u,    // kernel policy: BVH walks of a CTA are compacted through a shared-memory ray queue (pt_kernels.cuh)
     PT_F_COOP = 512u,     // kernel policy: sparse BVH walks (few lanes of the warp) are traced one ray at a time by all 32 lanes
     PT_F_LENS = 128u      // thin-lens camera (-d, always in world 4); pinhole-only variants drop that code
 };

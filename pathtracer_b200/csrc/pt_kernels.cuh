@@ -21,28 +21,18 @@ __host__ __device__ constexpr int pt_render_min_blocks(uint32_t F) {
 }
 
 // k_render / k_render_wf instantiations, from specialised to general: the first whose mask covers the scene runs
-#ifdef PT_QUEUE_BVH          // experiment: CTA-level ray queue for the BVH walk
-#define PT_F_QUEUE_X PT_F_QUEUE
-#else
-#define PT_F_QUEUE_X 0u
-#endif
-#ifdef PT_DEFER_ALL          // experiment: shade deferral for every family (tools/build_variants.sh "128 8 -DPT_DEFER_ALL")
-#define PT_F_DEFER_X PT_F_DEFER
-#else
-#define PT_F_DEFER_X 0u
-#endif
 #define PT_RENDER_VARIANTS(X) \
-    X(PT_F_TEX | PT_F_LIGHT | PT_F_DEFER) X(PT_F_SPH_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_QUEUE_X) X(PT_F_QUADS | PT_F_LIGHT | PT_F_DEFER_X) X(PT_F_SPH_BVH | PT_F_LENS | PT_F_DEFER_X | PT_F_QUEUE_X) \
-    X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_QUEUE_X) /* the same families with -d */ X(PT_F_TEX | PT_F_LIGHT | PT_F_DEFER | PT_F_LENS) \
-    X(PT_F_SPH_BVH | PT_F_LIGHT | PT_F_LENS | PT_F_DEFER) X(PT_F_QUADS | PT_F_LIGHT | PT_F_LENS | PT_F_DEFER_X) X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_LENS) \
+    X(PT_F_TEX | PT_F_LIGHT | PT_F_DEFER) X(PT_F_SPH_BVH | PT_F_LIGHT | PT_F_DEFER) X(PT_F_QUADS | PT_F_LIGHT) X(PT_F_SPH_BVH | PT_F_LENS) \
+    X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER) /* the same families with -d */ X(PT_F_TEX | PT_F_LIGHT | PT_F_DEFER | PT_F_LENS) \
+    X(PT_F_SPH_BVH | PT_F_LIGHT | PT_F_LENS | PT_F_DEFER) X(PT_F_QUADS | PT_F_LIGHT | PT_F_LENS) X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_LENS) \
     X(PT_F_ALL | PT_F_DEFER)
 // megakernel only: the same families with PT_F_COOP (sparse walks traced warp-cooperatively); launched when the scene's
-// one tree has a cluster cut and the threshold is > 0 (default: triangle trees, 12 lanes; PT_COOP_MAX overrides)
+// one tree has a cluster cut and the threshold is > 0 (default: triangle trees, 12 lanes; pt_tuning.coop_max overrides)
 #define PT_RENDER_COOP_VARIANTS(X) \
     X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_COOP) X(PT_F_SPH_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_COOP) \
-    X(PT_F_SPH_BVH | PT_F_LENS | PT_F_DEFER_X | PT_F_COOP) X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_LENS | PT_F_COOP)
+    X(PT_F_SPH_BVH | PT_F_LENS | PT_F_COOP) X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_LENS | PT_F_COOP)
 
-#define PT_N_COUNTERS 72            // [0] rays [1] NaN retries [2] samples [3] -, then the PT_STATS_HIST experiment's histograms
+#define PT_N_COUNTERS 4             // [0] rays [1] NaN retries [2] samples dropped after PT_MAX_NAN_RETRIES [3] -
 
 struct PtRenderArgs {
     int width, height, pp;
@@ -56,9 +46,7 @@ struct PtRenderArgs {
     uint64_t seed;
     float4 *accum;                      // width*height: sum r,g,b + number of samples
     unsigned long long *counters;       // [0] rays, [1] NaN retries, [2] samples
-    uint32_t coop_max;                  // PT_F_COOP variants: walks entered by <= coop_max lanes are traced cooperatively (last: keeps offsets)
-    uint32_t min_trace;                 // -DPT_X_SHADE_RULE builds only (PT_SHADE_MIN_TRACE, default 1 = the product rule)
-    uint32_t philox_k[20];              // -DPT_X_PHILOX_KEYS builds only: round keys of the render seed, (k0_r, k1_r) for r = 0..9
+    uint32_t coop_max;                  // PT_F_COOP variants: walks entered by <= coop_max lanes are traced cooperatively
 };
 
 // ---- camera (RenderTexel's two sampling loops, src/win32_main.cpp:1032-1170) ----------------------
@@ -151,16 +139,28 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
     const int y = (int)(ty + (gy << ph_log2) + (pig >> pw_log2));
     active = active && x < A.width && y < A.height;
 
-    uint32_t s = active ? A.s_begin + sl : A.s_end;
     const PtPixelCam pxc = pt_pixel_cam(A.width, A.height, A.pp, x, y);
     uint32_t retry = 0, n_acc = 0, n_rays = 0, n_nan = 0;
     // Per-pixel sums in a CANONICAL order, whatever the launch shape: sample s belongs to logical lane
-    // (s - s_begin) % 32; a physical lane owns 32/S logical lanes and keeps one accumulator for each (local
-    // memory, touched once per finished sample); at the end they are added in the order of a 32-lane xor
-    // butterfly.  So S = 8 (full frames) and S = 32 (small multi-GPU shares) give bit-identical pixels.
+    // (s - s_begin) % 32, a logical lane adds its samples in increasing order, and the 32 partial sums are added in the
+    // order of a 32-lane xor butterfly.  A physical lane owns the 32/S logical lanes sl, sl + S, ...; it works through
+    // them ONE AFTER THE OTHER (samples s, s + 32, s + 64, ... of one logical lane, then the next), so the running sum
+    // lives in three registers and only a finished logical lane is stored (accl: local memory, 32/S stores per pixel
+    // instead of a load + store per sample).  So S = 8 (full frames) and S = 32 (small multi-GPU shares) give
+    // bit-identical pixels.
+    const uint32_t n_logical = 32u >> lS;
+    uint32_t k_log = 0;                                    // the logical lane in progress: sl + k_log * S
+    uint32_t s = active ? A.s_begin + sl : A.s_end;
+    float3 acc_cur = f3(0, 0, 0);
     float accl[32][3];
 #pragma unroll 1
-    for (uint32_t k = 0; k < (32u >> lS); k++) accl[k][0] = accl[k][1] = accl[k][2] = 0.f;
+    for (uint32_t k = 0; k < n_logical; k++) accl[k][0] = accl[k][1] = accl[k][2] = 0.f;
+    // the sample after s in this lane's order; >= s_end when the lane has none left
+    auto next_sample = [&](uint32_t cur, uint32_t k) -> uint32_t {
+        uint32_t n = cur + 32u;
+        if (n >= A.s_end) n = (k + 1u < n_logical) ? A.s_begin + sl + (k + 1u) * Sn : A.s_end;
+        return n;
+    };
     float3 o = f3(0, 0, 0), d = f3(0, 0, 1), beta = f3(1, 1, 1), L = f3(0, 0, 0);
     int depth = 0;
     PtHit h;
@@ -168,9 +168,6 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
     h.id = PT_ID_MISS;
     PtRng rng;
     rng.init(A.seed, 0, 0, 0);
-#ifdef PT_X_PHILOX_KEYS
-    rng.K = A.philox_k;
-#endif
 
     // Lane states.  Where only ~30 % of the segments continue with a BRDF sample (w1, w5), shading right
     // after the trace runs the longest straight-line code of the kernel at a third of the lanes.  With
@@ -183,19 +180,7 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
     enum { NO_RAY = 0, NEW_RAY = 1, NEED_SHADE = 2 };
     uint32_t state = NO_RAY;
 
-    // PT_F_QUEUE: the BVH walks of the whole CTA go through a shared-memory ray queue.  Every lane does the cheap
-    // front end of the closest hit itself (linear lists + "does the ray enter the root?"); rays that enter are
-    // written to the queue at ballot/atomic-compacted slots, and after a barrier thread k walks ray k -- full warps
-    // however sparsely the rays were spread over the CTA's lanes -- and leaves (t, id) in the slot for the owner.
-    constexpr bool kQueue = (F & PT_F_QUEUE) && (((F & PT_F_SPH_BVH) != 0) != ((F & PT_F_TRI_BVH) != 0));
-    constexpr bool kCoop = !kQueue && (F & PT_F_COOP) && (((F & PT_F_SPH_BVH) != 0) != ((F & PT_F_TRI_BVH) != 0));
-    __shared__ float4 q_o[kQueue ? PT_RENDER_THREADS : 1], q_d[kQueue ? PT_RENDER_THREADS : 1];
-    __shared__ uint32_t q_n[2];
-    uint32_t q_iter = 0;
-    if (kQueue) {
-        if (threadIdx.x < 2) q_n[threadIdx.x] = 0;
-        __syncthreads();
-    }
+    constexpr bool kCoop = (F & PT_F_COOP) && (((F & PT_F_SPH_BVH) != 0) != ((F & PT_F_TRI_BVH) != 0));
 
     while (true) {
         if (state == NO_RAY && s < A.s_end) {
@@ -208,49 +193,7 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
             state = NEW_RAY;
         }
         const uint32_t n_live = __popc(__ballot_sync(0xffffffffu, state != NO_RAY));
-        if (!kQueue && n_live == 0) break;
-
-        if (kQueue) {
-            bool deep = false;
-            if (state == NEW_RAY) {
-                h.t = 3.402823466e+38f;
-                h.id = PT_ID_MISS;
-                pt_hit_analytic<F>(S, o, d, pt_dot_exact(d), h);
-                deep = pt_bvh_root_hit((F & PT_F_TRI_BVH) ? S.tri_bvh : S.sphere_bvh, pt_ray_inv(o, d), h.t);
-            }
-            const uint32_t par = q_iter & 1u;
-            const uint32_t m = __ballot_sync(0xffffffffu, deep);
-            uint32_t slot = 0;
-            if (m != 0u) {
-                const int leader = __ffs((int)m) - 1;
-                if ((int)lane == leader) slot = atomicAdd(&q_n[par], (uint32_t)__popc(m));
-                slot = __shfl_sync(0xffffffffu, slot, leader) + __popc(m & ((1u << lane) - 1u));
-            }
-            if (deep) {
-                q_o[slot] = make_float4(o.x, o.y, o.z, h.t);
-                q_d[slot] = make_float4(d.x, d.y, d.z, __uint_as_float(h.id));
-            }
-            if (!__syncthreads_or(n_live != 0)) break;            // whole CTA finished
-            const uint32_t nq = q_n[par];
-            if (threadIdx.x == 0) q_n[par ^ 1u] = 0;
-            if (threadIdx.x < nq) {
-                const float4 qo = q_o[threadIdx.x], qd = q_d[threadIdx.x];
-                PtHit hh;
-                hh.t = qo.w;
-                hh.id = __float_as_uint(qd.w);
-                const float3 ro = f3(qo.x, qo.y, qo.z), rd = f3(qd.x, qd.y, qd.z);
-                if (F & PT_F_TRI_BVH) pt_bvh_walk<PT_LEAF_TRIS>(S, S.tri_bvh, ro, rd, pt_dot_exact(rd), hh);
-                else pt_bvh_walk<PT_LEAF_SPHERES>(S, S.sphere_bvh, ro, rd, pt_dot_exact(rd), hh);
-                q_o[threadIdx.x].w = hh.t;
-                q_d[threadIdx.x].w = __uint_as_float(hh.id);
-            }
-            __syncthreads();
-            if (deep) {
-                h.t = q_o[slot].w;
-                h.id = __float_as_uint(q_d[slot].w);
-            }
-            q_iter++;
-        }
+        if (n_live == 0) break;
 
         // PT_F_COOP: every new ray does the linear lists and the root step itself; then the warp votes.  When few lanes
         // enter the tree (bounce rays that cross the mesh's box while their neighbours see sky or ground -- 2/3 of the
@@ -290,10 +233,7 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
         // ---- closest hit, emission, termination rules of RayCast (main.cpp:579-590, 799) ----
         bool done = false;
         if (state == NEW_RAY) {
-#ifdef PT_STATS_HIST
-            g_pt_hist = A.counters;
-#endif
-            if (!kQueue && !kCoop) h = pt_closest_hit<F>(S, o, d);
+            if (!kCoop) h = pt_closest_hit<F>(S, o, d);
             n_rays++;
             float3 n;
             uint32_t mat;
@@ -315,12 +255,12 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
         if (F & PT_F_DEFER) {
             __syncwarp();
             const uint32_t nS = __popc(__ballot_sync(0xffffffffu, state == NEED_SHADE && !done));
-            const uint32_t nD = __popc(__ballot_sync(0xffffffffu, done && s + Sn < A.s_end));   // lanes that will regenerate
-#ifdef PT_X_SHADE_RULE      // experiment build: also shade when fewer than min_trace lanes would trace in the next iteration (nD == 0 generalised)
-            if (nS >= A.shade_batch || nD < A.min_trace) {
+#ifdef PT_X_OLD_ACCL
+            const uint32_t nD = __popc(__ballot_sync(0xffffffffu, done && s + Sn < A.s_end));
 #else
-            if (nS >= A.shade_batch || nD == 0) {
+            const uint32_t nD = __popc(__ballot_sync(0xffffffffu, done && next_sample(s, k_log) < A.s_end));   // lanes that will regenerate
 #endif
+            if (nS >= A.shade_batch || nD == 0) {
                 if (state == NEED_SHADE && !done) {
                     float3 n;
                     uint32_t mat;
@@ -338,13 +278,27 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
                 retry++;                                                    // redraw this sample, main.cpp:1068
                 n_nan++;
             } else {
-                if (isnan3(L)) L = f3(0, 0, 0);
-                const uint32_t k = ((s - A.s_begin) >> lS) & ((32u >> lS) - 1u);
-                accl[k][0] += L.x;
-                accl[k][1] += L.y;
-                accl[k][2] += L.z;
+                if (isnan3(L)) {                                            // still NaN after the redraws: black, and reported (pt_stats.nan_dropped)
+                    L = f3(0, 0, 0);
+                    if (A.counters) atomicAdd(A.counters + 2, 1ull);
+                }
+#ifdef PT_X_OLD_ACCL      // A/B switch for one measurement (round-1 order of execution: lane strides by S, sums indexed per sample)
+                const uint32_t kk = ((s - A.s_begin) >> lS) & (n_logical - 1u);
+                accl[kk][0] += L.x; accl[kk][1] += L.y; accl[kk][2] += L.z;
+                n_acc++; s += Sn; retry = 0;
+                continue;
+#endif
+                acc_cur = acc_cur + L;
                 n_acc++;
-                s += Sn;
+                const uint32_t sn = next_sample(s, k_log);
+                if (s + 32u >= A.s_end) {                                   // this logical lane is complete
+                    accl[k_log][0] = acc_cur.x;
+                    accl[k_log][1] = acc_cur.y;
+                    accl[k_log][2] = acc_cur.z;
+                    acc_cur = f3(0, 0, 0);
+                    k_log++;
+                }
+                s = sn;
                 retry = 0;
             }
         }
@@ -499,6 +453,41 @@ __global__ void k_unpack_tiles(uint32_t *__restrict__ bgra, const uint32_t *__re
     uint32_t tile = rank + j * count;
     int x = (int)((tile % tiles_x) * PT_TILE + (p & 31u)), y = (int)((tile / tiles_x) * PT_TILE + (p >> 5));
     if (x < W && y < H) bgra[(size_t)y * W + x] = packed[i];
+}
+
+// resolve + pack in one pass: own tile j -> packed[j*1024 ..], resolved from the accumulator (no full-frame resolve first)
+__global__ void k_resolve_pack_tiles(const float4 *__restrict__ accum, uint32_t *__restrict__ packed, int W, int H,
+                                     uint32_t tiles_x, uint32_t rank, uint32_t count, uint32_t n_my_tiles) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_my_tiles * 1024u) return;
+    uint32_t j = i >> 10, p = i & 1023u;
+    uint32_t tile = rank + j * count;
+    int x = (int)((tile % tiles_x) * PT_TILE + (p & 31u)), y = (int)((tile / tiles_x) * PT_TILE + (p >> 5));
+    uint32_t v = 0u;
+    if (x < W && y < H) {
+        float4 a = accum[(size_t)y * W + x];
+        float inv = a.w > 0.f ? __fdiv_rn(1.0f, a.w) : 0.f;
+        v = pt_resolve_pixel(__fmul_rn(a.x, inv), __fmul_rn(a.y, inv), __fmul_rn(a.z, inv));
+    }
+    packed[i] = v;
+}
+// scatter the packs of ALL ranks (gathered back to back, `stride` words per rank) into the frame: one thread per pixel
+__global__ void k_unpack_gathered(uint32_t *__restrict__ bgra, const uint32_t *__restrict__ gathered, int W, int H,
+                                  uint32_t tiles_x, uint32_t count, uint32_t stride) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (uint32_t)W * (uint32_t)H) return;
+    uint32_t x = i % (uint32_t)W, y = i / (uint32_t)W;
+    uint32_t tile = (y / PT_TILE) * tiles_x + x / PT_TILE;
+    uint32_t r = tile % count, j = tile / count;
+    bgra[i] = gathered[(size_t)r * stride + j * 1024u + (y % PT_TILE) * PT_TILE + (x % PT_TILE)];
+}
+// resolve n pixels from any accumulator to any BGRA buffer (a rank's share after a reduce-scatter)
+__global__ void k_resolve_range(const float4 *__restrict__ accum, uint32_t *__restrict__ bgra, uint32_t n) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 a = accum[i];
+    float inv = a.w > 0.f ? __fdiv_rn(1.0f, a.w) : 0.f;
+    bgra[i] = pt_resolve_pixel(__fmul_rn(a.x, inv), __fmul_rn(a.y, inv), __fmul_rn(a.z, inv));
 }
 
 // resolve this rank's tiles straight into a BGRA frame that may live on another GPU (mapped peer memory): thread i

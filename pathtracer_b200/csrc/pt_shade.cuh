@@ -124,11 +124,12 @@ __device__ __forceinline__ bool pt_shade_vertex(const PtDeviceScene &S, PtRng &r
     const bool use_light = (F & PT_F_LIGHT) && !(S.flags & PT_SCENE_JUST_COSINE);   // main.cpp:654-655
 
     float3 L, H = f3(0, 0, 0);
-    float px = 1.f;
+    float px;
     bool specular;
     int guard = 0;
     for (;;) {
         if (++guard > 64) return false;      // the reference would spin (origin inside the light); give up
+        px = 1.f;                            // both specular branches set it every iteration (main.cpp:674, 730)
         const uint4 u = rng.next_block();    // one Philox block per iteration: coin, then [coin, r1, r2] or [z1, z2]
         specular = u32_to_unit(u.x) > 0.5f;                                  // main.cpp:661
         if (specular && smooth) {

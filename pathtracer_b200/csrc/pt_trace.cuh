@@ -76,20 +76,10 @@ __device__ __forceinline__ void pt_accept(PtHit &h, float t, uint32_t id) {
 enum { PT_LEAF_SPHERES = 0, PT_LEAF_TRIS = 1 };
 #define PT_STACK_SENTINEL ((int)0x80000000)
 
-// The per-lane traversal stack.  Default: a thread-local array (local memory: L1-resident, stores write through to L2).
-// -DPT_X_SMEM_STACK (experiment build, tools/r02_experiments.sh): one column per thread of a shared-memory array, 32
-// entries deep (16 KB per 128-thread CTA; pt_upload_scene of that build rejects deeper trees), conflict-free.
-#ifdef PT_X_SMEM_STACK
-#define PT_X_SMEM_STACK_DEPTH 32
-__shared__ int pt_s_stack[PT_X_SMEM_STACK_DEPTH][128];      // one array per kernel, whichever walks it inlines (all launch 128 threads)
-#define PT_DECLARE_STACK
-#define PT_STK(i) pt_s_stack[(i)][threadIdx.x & 127u]
-#define PT_WALK_STACK_LIMIT PT_X_SMEM_STACK_DEPTH
-#else
+// The per-lane traversal stack: a thread-local array (local memory: L1-resident, stores write through to L2).
 #define PT_DECLARE_STACK int stack[PT_STACK_DEPTH]
 #define PT_STK(i) stack[(i)]
 #define PT_WALK_STACK_LIMIT PT_STACK_DEPTH
-#endif
 
 __device__ __forceinline__ float pt_rcp_approx(float x) {
     float r;
@@ -163,17 +153,9 @@ __device__ __forceinline__ void pt_leaf_test(const PtDeviceScene &S, int node, f
 
 // Stack-based BVH2 walk in "while-while" form: every lane first descends inner nodes until it holds a
 // leaf (nearer child first, culled by the best t so far), then the lanes test their leaves together.
-#ifdef PT_STATS_HIST
-__device__ unsigned long long *g_pt_hist;     // experiment build only
-#endif
 template <int LEAF, bool BARE_RCP = true>
 __device__ __forceinline__ void pt_bvh_walk(const PtDeviceScene &S, const PtBvh &bvh, float3 o, float3 d, float a, PtHit &h) {
     const PtRayInv r = pt_ray_inv<BARE_RCP>(o, d);
-#ifdef PT_STATS_HIST
-    const bool enters = pt_bvh_root_hit(bvh, r, h.t);
-    const uint32_t n_enter = __popc(__ballot_sync(__activemask(), enters));
-    uint32_t my_steps = 0;
-#endif
     PT_DECLARE_STACK;
     PT_STK(0) = PT_STACK_SENTINEL;
     int sp = 1;
@@ -181,9 +163,6 @@ __device__ __forceinline__ void pt_bvh_walk(const PtDeviceScene &S, const PtBvh 
     const float4 *nodes = reinterpret_cast<const float4 *>(bvh.nodes);
     while (node != PT_STACK_SENTINEL) {
         while (node >= 0) {
-#ifdef PT_STATS_HIST
-            my_steps++;
-#endif
             const float4 b0 = __ldg(nodes + 4 * node), b1 = __ldg(nodes + 4 * node + 1), b2 = __ldg(nodes + 4 * node + 2);
             const int4 link = __ldg(reinterpret_cast<const int4 *>(nodes + 4 * node + 3));
             bool hl, hr;
@@ -202,12 +181,6 @@ __device__ __forceinline__ void pt_bvh_walk(const PtDeviceScene &S, const PtBvh 
             node = PT_STK(--sp);
         }
     }
-#ifdef PT_STATS_HIST
-    if (enters && g_pt_hist) {
-        atomicAdd(g_pt_hist + 4 + n_enter, 1ull);
-        atomicAdd(g_pt_hist + 4 + 33 + n_enter, (unsigned long long)my_steps);
-    }
-#endif
 }
 
 // The same walk as a resumable object: advance() descends to the next leaf, tests it and pops.  A lane can

@@ -4,19 +4,20 @@ The reference's only parallelism is CPU threads over 32x32 tiles handed out by M
 (src/win32_main.cpp:888-960).  Two partitions of the same work, both with exactly one exchange:
 
   * "tiles"   rank r renders the tiles t with t % G == r (interleaved, so sky tiles and Mario tiles
-              spread evenly), resolves them, packs them tile-major and the packs are GATHERED to
-              rank 0 (4 B/pixel in total, no reduction).  Counter-based RNG keyed by (pixel, sample)
-              => the frame is bit-identical for any G.
+              spread evenly) and resolves them straight into a tile-major pack (pt_resolve_pack_tiles);
+              the packs are GATHERED into one contiguous buffer on rank 0 (4 B/pixel in total, no
+              reduction) and scattered into the frame by ONE kernel (pt_unpack_gathered).  Counter-based
+              RNG keyed by (pixel, sample) => the frame is bit-identical for any G.
   * "samples" rank r renders samples [r*spp/G, (r+1)*spp/G) of every pixel into its float4
-              accumulation buffer; one REDUCE(sum, fp32) to rank 0, which resolves.
-
+              accumulation buffer.  REDUCE-SCATTER(sum, fp32) leaves rank r with the sums of pixels
+              [r*n/G, (r+1)*n/G); it resolves them (pt_resolve_range) and the 4 B/pixel results are
+              gathered straight into rank 0's frame.  (Where n % G != 0, or on a backend without
+              reduce-scatter: one REDUCE to rank 0, which resolves.)
   * "tiles_p2p" the same partition as "tiles", exchanged without a collective on the data path: rank 0 exports
               its BGRA frame as a CUDA IPC handle once, the other ranks map it, and every rank's resolve kernel
               stores its tiles straight into that frame over NVLink (pt_resolve_tiles_to) -- resolve + pack +
               gather + unpack become one kernel per rank.  Two stream-ordered one-word all-reduces per frame
               order the ranks: (A) rank 0 has finished with the previous frame, (B) every rank's tiles have landed.
-              (CUDA only: written at the end of round 1 without a GPU at hand, opt-in until tools/p2p_check.py has
-              run on a multi-GPU box.)
 
 The collectives run on torch tensors, so the same code runs on NCCL (GPU) and on gloo (CPU tests,
 where the render step is injected).  Nothing here does render arithmetic.
@@ -72,9 +73,17 @@ def unpack_tiles_host(bgra, packed, rank, world):
     return bgra
 
 
-def gather_packed_tiles(packed, width, height, group=None):
-    """Gather every rank's packed tiles ([n_r*1024] int32 tensor) to rank 0.
-    Returns the list of per-rank tensors on rank 0 (padded to the same length), else None."""
+def unpack_gathered_host(gathered, width, height, world):
+    """numpy mirror of k_unpack_gathered: `gathered` is [world, n_max*1024] uint32, rank r's pack in row r."""
+    tx, _ = tile_grid(width, height)
+    y, x = np.mgrid[0:height, 0:width]
+    tile = (y // TILE) * tx + x // TILE
+    return gathered[tile % world, (tile // world) * (TILE * TILE) + (y % TILE) * TILE + (x % TILE)]
+
+
+def gather_packed_tiles(packed, width, height, group=None, out=None):
+    """Gather every rank's packed tiles ([n_r*1024] int32 tensor) into ONE contiguous [world, n_max*1024] tensor on
+    rank 0 (`out` if given); returns it there, None elsewhere."""
     import torch
     import torch.distributed as dist
     world = dist.get_world_size(group) if dist.is_initialized() else 1
@@ -83,10 +92,11 @@ def gather_packed_tiles(packed, width, height, group=None):
     if packed.numel() < n_max:
         packed = torch.cat([packed, packed.new_zeros(n_max - packed.numel())])
     if world == 1:
-        return [packed]
-    bufs = [torch.empty_like(packed) for _ in range(world)] if rank == 0 else None
-    dist.gather(packed, bufs, dst=0, group=group)
-    return bufs
+        return packed.view(1, n_max)
+    if rank == 0 and out is None:
+        out = packed.new_empty((world, n_max))
+    dist.gather(packed, list(out.unbind(0)) if rank == 0 else None, dst=0, group=group)
+    return out if rank == 0 else None
 
 
 def reduce_accum(accum, group=None):
@@ -95,6 +105,35 @@ def reduce_accum(accum, group=None):
     if dist.is_initialized() and dist.get_world_size(group) > 1:
         dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM, group=group)
     return accum
+
+
+def pixel_share(n_pixels, rank, world):
+    """[lo, hi) of the pixel list owned by `rank` after the reduce-scatter; None when it does not divide evenly."""
+    if world < 1 or n_pixels % world:
+        return None
+    c = n_pixels // world
+    return rank * c, (rank + 1) * c
+
+
+def reduce_scatter_accum(accum_flat, out, group=None):
+    """out <- this rank's share of the element-wise sum of every rank's accum_flat (len(accum_flat) = world*len(out)).
+    NCCL: one reduce-scatter.  gloo has none: all-reduce a copy and slice (CPU tests of the partition)."""
+    import torch.distributed as dist
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    if dist.get_backend(group) == "nccl":
+        dist.reduce_scatter_tensor(out, accum_flat, op=dist.ReduceOp.SUM, group=group)
+    else:
+        t = accum_flat.clone()
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+        out.copy_(t.view(world, -1)[rank])
+    return out
+
+
+def gather_shares(mine, frame_flat, group=None):
+    """Gather every rank's resolved share (`mine`, equal lengths) into rank 0's flat frame, in rank order."""
+    import torch.distributed as dist
+    rank = dist.get_rank(group)
+    dist.gather(mine, list(frame_flat.split(mine.numel())) if rank == 0 else None, dst=0, group=group)
 
 
 class ShardedFrame:
@@ -108,17 +147,24 @@ class ShardedFrame:
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.torch = torch
-        self._packed = None
+        self._packed = self._gathered = self._share = None
         self.launches = 0
         self._remote = None          # tiles_p2p: rank 0's frame mapped into this process
         self._flag = None
+        self.phase_events = None     # a list: render() appends a CUDA event recorded right after the render launch (bench.py)
+
+    def _mark_rendered(self):
+        if self.phase_events is not None:
+            ev = self.torch.cuda.Event(enable_timing=True)
+            ev.record()
+            self.phase_events.append(ev)
 
     def _p2p_setup(self):
         """Once per frame size: rank 0 exports its BGRA frame, everybody else maps it."""
         import torch.distributed as dist
         torch, core = self.torch, self.core
         self._flag = torch.zeros(1, dtype=torch.int32, device="cuda")
-        h = torch.zeros(72, dtype=torch.uint8, device="cuda")      # PT_IPC_HANDLE_BYTES
+        h = torch.zeros(80, dtype=torch.uint8, device="cuda")      # PT_IPC_HANDLE_BYTES
         if self.rank == 0:
             raw = core.frame_ipc_handle(self.w, self.h)
             h.copy_(torch.frombuffer(bytearray(raw), dtype=torch.uint8))
@@ -142,6 +188,7 @@ class ShardedFrame:
             if not getattr(self, "_p2p_ready", False):
                 self._p2p_setup()
             core.render(self.w, self.h, pp, seed=seed, tile_rank=self.rank, tile_count=self.world)
+            self._mark_rendered()
             if self.world > 1:
                 dist.all_reduce(self._flag, group=self.group)      # (A) rank 0's stream is past everything that read the previous frame
             core.resolve_tiles_to(self._remote if self.rank != 0 else None, self.rank, self.world)
@@ -154,22 +201,24 @@ class ShardedFrame:
             return torch.as_tensor(b, device="cuda")
         if self.mode == "tiles":
             core.render(self.w, self.h, pp, seed=seed, tile_rank=self.rank, tile_count=self.world)
-            core.resolve()
-            self.launches += 2
+            self._mark_rendered()
             if self.world == 1:
+                core.resolve()
+                self.launches += 2
                 _, b = core.device_buffers()
                 return torch.as_tensor(b, device="cuda")
             n_max = max_tiles_per_rank(self.w, self.h, self.world) * TILE * TILE
             if self._packed is None:
                 self._packed = torch.zeros(n_max, dtype=torch.int32, device="cuda")
-            core.pack_tiles(self._packed.data_ptr(), self.rank, self.world)
-            self.launches += 1
-            bufs = gather_packed_tiles(self._packed, self.w, self.h, self.group)
+                if self.rank == 0:
+                    self._gathered = torch.zeros((self.world, n_max), dtype=torch.int32, device="cuda")
+            core.resolve_pack_tiles(self._packed.data_ptr(), self.rank, self.world)     # resolve of my tiles only, tile-major
+            self.launches += 2
+            gather_packed_tiles(self._packed, self.w, self.h, self.group, out=self._gathered)
             if self.rank != 0:
                 return None
-            for r in range(1, self.world):
-                core.unpack_tiles(bufs[r].data_ptr(), r, self.world)
-                self.launches += 1
+            core.unpack_gathered(self._gathered.data_ptr(), self.world, n_max)           # every rank's tiles in one kernel
+            self.launches += 1
             _, b = core.device_buffers()
             return torch.as_tensor(b, device="cuda")
         lo, hi = sample_range(pp, self.rank, self.world)
@@ -177,12 +226,28 @@ class ShardedFrame:
             core.render(self.w, self.h, pp, seed=seed, sample_begin=lo, sample_end=hi)
         else:
             core.render(self.w, self.h, 0, seed=seed)      # more ranks than samples: contribute zeros
+        self._mark_rendered()
         self.launches += 1
         a, b = core.device_buffers()
         acc = torch.as_tensor(a, device="cuda")
+        frame = torch.as_tensor(b, device="cuda")
+        share = pixel_share(self.w * self.h, self.rank, self.world)
+        if self.world > 1 and share is not None:
+            n = share[1] - share[0]
+            if self._share is None:
+                self._share = torch.empty(n * 4, dtype=torch.float32, device="cuda")
+            reduce_scatter_accum(acc.view(-1), self._share, self.group)
+            mine = frame.view(-1)[share[0]:share[1]]
+            core.resolve_range(self._share.data_ptr(), mine.data_ptr(), n)               # my share of the pixels
+            self.launches += 1
+            gather_shares(mine, frame.view(-1), self.group)
+            if self.rank != 0:
+                return None
+            core.mark_resolved()
+            return frame
         reduce_accum(acc, self.group)
         if self.rank != 0:
             return None
         core.resolve()
         self.launches += 1
-        return torch.as_tensor(b, device="cuda")
+        return frame

@@ -2,7 +2,12 @@
 //
 //   image_compare a.bmp b.bmp            legacy "Percentage Similarity" + RMSE + PSNR + max abs difference
 //   image_compare --hdr a.hdr.bin b.hdr.bin [--sigma 3]
-//                                        per-pixel z-test of two float accumulator dumps (pathtracer --hdr)
+//                                        two float accumulator dumps (pathtracer --hdr): HDR RMSE, bias, outliers against the
+//                                        pooled difference; and, when BOTH dumps carry the optional second plane (per pixel
+//                                        and channel: the variance of the mean, i.e. the squared standard error), the
+//                                        per-pixel z-test of BASELINE.json's north_star: z = (a - b) / sqrt(se_a^2 + se_b^2),
+//                                        fraction of |z| > sigma, mean z, and the global z of the image mean
+//                                        (tools/parity_report.py writes such dumps for the reference and for this renderer)
 //
 // The legacy number is kept BUG-COMPATIBLE and labelled so: the reference's Magnitude() (image_compare.c:121-124)
 // is sqrt(a*a + b*b + g*g + a*a) -- red is never compared and alpha is counted twice -- on channels scaled to
@@ -18,7 +23,9 @@
 
 static void usage() { std::printf("usage: image_compare image_file1 image_file2 [--hdr] [--sigma S]\n"); }   // image_compare.c:146-149
 
-static bool read_hdr(const char *path, int &w, int &h, std::vector<float> &v) {
+// dump layout: int32 width, height; width*height float4 (sum r, g, b, sample count); optionally a second plane of
+// width*height float4 (variance of the mean of r, g, b; unused)
+static bool read_hdr(const char *path, int &w, int &h, std::vector<float> &v, std::vector<float> &var) {
     FILE *f = std::fopen(path, "rb");
     if (!f) return false;
     int32_t hd[2];
@@ -27,6 +34,10 @@ static bool read_hdr(const char *path, int &w, int &h, std::vector<float> &v) {
         w = hd[0]; h = hd[1];
         v.resize((size_t)w * h * 4);
         ok = std::fread(v.data(), sizeof(float), v.size(), f) == v.size();
+        if (ok) {
+            var.resize(v.size());
+            if (std::fread(var.data(), sizeof(float), var.size(), f) != var.size()) var.clear();
+        }
     }
     std::fclose(f);
     return ok;
@@ -49,9 +60,9 @@ int main(int argc, char **argv) {
         // ~ |mean| / sqrt(n) at best; without per-sample variance in the dump the test uses the pooled difference
         // variance of the image as the noise scale and reports the fraction of outliers beyond `sigma`.
         int w1, h1, w2, h2;
-        std::vector<float> a, b;
-        if (!read_hdr(p1, w1, h1, a)) { std::printf("Error: '%s' is an invalid file path\n", p1); return -1; }
-        if (!read_hdr(p2, w2, h2, b)) { std::printf("Error: '%s' is an invalid file path\n", p2); return -1; }
+        std::vector<float> a, b, va, vb;
+        if (!read_hdr(p1, w1, h1, a, va)) { std::printf("Error: '%s' is an invalid file path\n", p1); return -1; }
+        if (!read_hdr(p2, w2, h2, b, vb)) { std::printf("Error: '%s' is an invalid file path\n", p2); return -1; }
         if (w1 != w2) { std::printf("Error: Images must have same width but they are %d and %d\n", w1, w2); return -1; }
         if (h1 != h2) { std::printf("Error: Images must have same height but they are %d and %d\n", h1, h2); return -1; }
         const size_t n = (size_t)w1 * h1;
@@ -72,6 +83,23 @@ int main(int argc, char **argv) {
         std::printf("HDR RMSE: %.6f  bias (mean difference): %.3e = %.2f standard errors\n", std::sqrt(sum_d2 / N), mean_d,
                     sd > 0 ? mean_d / (sd / std::sqrt(N)) : 0.0);
         std::printf("Outliers beyond %.1f sigma: %.4f %%\n", sigma, 100.0 * (double)out / N);
+        if (!va.empty() && !vb.empty()) {
+            // per-pixel, per-channel z-test against the sample standard errors of the two estimates; a relative 1e-5 floor
+            // keeps pixels that are constant on both sides (sky) from dividing a float rounding difference by zero
+            size_t beyond = 0;
+            double sz = 0, sz2 = 0, sd_all = 0, sv_all = 0;
+            for (size_t i = 0; i < n; i++)
+                for (int c = 0; c < 3; c++) {
+                    double ma = a[4 * i + 3] > 0 ? a[4 * i + c] / a[4 * i + 3] : 0.0, mb = b[4 * i + 3] > 0 ? b[4 * i + c] / b[4 * i + 3] : 0.0;
+                    double fl = 1e-5 * std::fmax(std::fabs(ma), std::fabs(mb));
+                    double v = (double)va[4 * i + c] + (double)vb[4 * i + c] + fl * fl + 1e-14;
+                    double z = (ma - mb) / std::sqrt(v);
+                    if (std::fabs(z) > sigma) beyond++;
+                    sz += z; sz2 += z * z; sd_all += ma - mb; sv_all += v;
+                }
+            std::printf("Per-pixel z-test (sample standard errors): |z| > %.1f on %.4f %% of pixel-channels   mean z: %.4f   rms z: %.4f   "
+                        "global z of the image mean: %.3f\n", sigma, 100.0 * (double)beyond / N, sz / N, std::sqrt(sz2 / N), sd_all / std::sqrt(sv_all));
+        }
         return 0;
     }
 

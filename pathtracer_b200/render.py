@@ -15,7 +15,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # PT_B200_LIB: another build of the same library (kernel experiments: tools/build_variants.sh)
 LIB_PATH = os.environ.get("PT_B200_LIB") or os.path.join(_HERE, "libpt_b200.so")
 
-IPC_HANDLE_BYTES = 72       # PT_IPC_HANDLE_BYTES
+IPC_HANDLE_BYTES = 80       # PT_IPC_HANDLE_BYTES
 _lib = None
 
 
@@ -38,6 +38,11 @@ def lib():
         L.pt_destroy.argtypes = [C.c_void_p]
         L.pt_upload_scene.argtypes = [C.c_void_p, C.POINTER(T.Scene)]
         L.pt_set_camera.argtypes = [C.c_void_p, C.POINTER(T.Camera)]
+        L.pt_set_tuning.argtypes = [C.c_void_p, C.POINTER(T.Tuning)]
+        L.pt_resolve_pack_tiles.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint32)]
+        L.pt_unpack_gathered.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]
+        L.pt_resolve_range.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32]
+        L.pt_mark_resolved.argtypes = [C.c_void_p]
         L.pt_render.argtypes = [C.c_void_p, C.POINTER(T.RenderParams)]
         L.pt_synchronize.argtypes = [C.c_void_p]
         L.pt_resolve.argtypes = [C.c_void_p]
@@ -67,7 +72,8 @@ EXPORTS = ["pt_api_version", "pt_create", "pt_destroy", "pt_last_error", "pt_upl
            "pt_render", "pt_synchronize", "pt_resolve", "pt_readback", "pt_device_buffers", "pt_set_stream",
            "pt_pack_tiles", "pt_unpack_tiles", "pt_gather_tiles_from", "pt_add_accum_from", "pt_trace_rays", "pt_primary_hits", "pt_trace_paths",
            "pt_resolve_colors", "pt_measure_fp32_peak", "pt_flush_l2",
-           "pt_frame_ipc_handle", "pt_open_peer_frame", "pt_close_peer_frame", "pt_resolve_tiles_to"]
+           "pt_frame_ipc_handle", "pt_open_peer_frame", "pt_close_peer_frame", "pt_resolve_tiles_to",
+           "pt_set_tuning", "pt_resolve_pack_tiles", "pt_unpack_gathered", "pt_resolve_range", "pt_mark_resolved"]
 
 
 def _p(a):
@@ -115,6 +121,13 @@ class RenderCore:
     def set_camera(self, cam):
         self._ck(lib().pt_set_camera(self._h, C.byref(cam)))
 
+    def set_tuning(self, sample_lanes_log2=-1, shade_batch=0, coop_max=-1, tri_leaf=0, sph_leaf=0, sah_sweep=-1,
+                   wf_pixels_log2=0):
+        """Scheduling knobs (pt_tuning): never change a sample.  coop_max / leaf sizes apply to the NEXT upload."""
+        t = T.Tuning(C.sizeof(T.Tuning), sample_lanes_log2, shade_batch, coop_max, tri_leaf, sph_leaf, sah_sweep,
+                     wf_pixels_log2)
+        self._ck(lib().pt_set_tuning(self._h, C.byref(t)))
+
     def set_stream(self, cuda_stream_ptr):
         self._ck(lib().pt_set_stream(self._h, cuda_stream_ptr))
 
@@ -154,6 +167,20 @@ class RenderCore:
 
     def unpack_tiles(self, src_ptr, tile_rank, tile_count):
         self._ck(lib().pt_unpack_tiles(self._h, src_ptr, tile_rank, tile_count))
+
+    def resolve_pack_tiles(self, dst_ptr, tile_rank, tile_count):
+        n = C.c_uint32()
+        self._ck(lib().pt_resolve_pack_tiles(self._h, dst_ptr, tile_rank, tile_count, C.byref(n)))
+        return n.value
+
+    def unpack_gathered(self, src_ptr, tile_count, stride_words):
+        self._ck(lib().pt_unpack_gathered(self._h, src_ptr, tile_count, stride_words))
+
+    def resolve_range(self, accum_ptr, bgra_ptr, n_pixels):
+        self._ck(lib().pt_resolve_range(self._h, accum_ptr, bgra_ptr, n_pixels))
+
+    def mark_resolved(self):
+        self._ck(lib().pt_mark_resolved(self._h))
 
     def flush_l2(self):
         self._ck(lib().pt_flush_l2(self._h))

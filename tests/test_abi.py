@@ -24,6 +24,15 @@ def test_pt_api_exports_every_declared_symbol():
     assert L.pt_api_version() == 1
 
 
+def test_release_library_reads_no_environment():
+    """Experiment switches live in the debug build (make -C pathtracer_b200/csrc debug, -DPT_DEBUG_ENV); the library a
+    host links holds no getenv of a PT_ name."""
+    import subprocess
+    from pathtracer_b200 import render
+    out = subprocess.run(["strings", render.LIB_PATH], capture_output=True, text=True).stdout.splitlines()
+    assert [s for s in out if re.fullmatch(r"PT_[A-Z0-9_]+", s)] == []
+
+
 def test_pt_host_exports_every_declared_symbol():
     from pathtracer_b200 import host
     L = host.lib()
@@ -36,6 +45,7 @@ def test_struct_sizes_match_header_contract():
     assert C.sizeof(T.Sphere) == 20 and C.sizeof(T.Aabb) == 52 and C.sizeof(T.Camera) == 116
     assert C.sizeof(T.Scene) == 8 * 4 + 7 * 8 + 4 * 16 + 116
     assert T.HIT_DTYPE.itemsize == 28
+    assert C.sizeof(T.Stats) == 56 and C.sizeof(T.Tuning) == 32 and C.sizeof(T.Config) == 24
 
 
 def test_render_core_fails_loudly_without_a_device():

@@ -47,6 +47,8 @@ def _worker(rank, world, port, mode, out_dir):
             for r in range(world):
                 n = len(D.my_tiles(W, H, r, world))
                 D.unpack_tiles_host(out, bufs[r].numpy().view(np.uint32)[:n * 1024].reshape(n, 32, 32), r, world)
+            # the one-kernel scatter of the whole gathered buffer (k_unpack_gathered) must give the same frame
+            assert np.array_equal(D.unpack_gathered_host(bufs.numpy().view(np.uint32), W, H, world), out)
             np.save(os.path.join(out_dir, "frame.npy"), out)
     else:
         lo, hi = D.sample_range(PP, rank, world)
@@ -56,6 +58,15 @@ def _worker(rank, world, port, mode, out_dir):
             acc[..., :3] = r["sum"]
             acc[..., 3] = hi - lo
         t = torch.from_numpy(acc)
+        share = D.pixel_share(W * H, rank, world)
+        if share is not None:
+            # reduce-scatter path: my share of the summed pixels, gathered in rank order = the full sum
+            mine = torch.empty((share[1] - share[0]) * 4)
+            D.reduce_scatter_accum(t.view(-1).clone(), mine, None)
+            full = torch.empty(W * H * 4) if rank == 0 else None
+            D.gather_shares(mine, full if rank == 0 else mine, None)
+            if rank == 0:
+                np.save(os.path.join(out_dir, "accum_rs.npy"), full.numpy().reshape(H, W, 4))
         D.reduce_accum(t)
         if rank == 0:
             np.save(os.path.join(out_dir, "accum.npy"), t.numpy())
@@ -80,6 +91,9 @@ def test_sharded_frame_over_gloo(tmp_path, world, mode):
         got = np.load(tmp_path / "accum.npy")
         assert (got[..., 3] == PP * PP).all()
         assert np.allclose(got[..., :3], full["sum"], rtol=1e-5, atol=1e-6)
+        if (W * H) % world == 0:
+            rs = np.load(tmp_path / "accum_rs.npy")
+            assert (rs[..., 3] == PP * PP).all() and np.allclose(rs[..., :3], got[..., :3], rtol=1e-6, atol=1e-7)
 
 
 def test_partitions_cover_exactly_once():

@@ -90,17 +90,16 @@ def test_sample_sharding_sums_to_full_frame(core, worlds):
 
 
 @pytest.mark.parametrize("lanes", [0, 1, 2, 3, 4, 5])
-def test_launch_shape_does_not_change_the_samples(worlds, lanes, monkeypatch):
+def test_launch_shape_does_not_change_the_samples(worlds, lanes):
     """S sample-lanes x P pixels per warp is a scheduling choice only: the kernel adds a pixel's samples in a
     canonical order (32 logical lanes, xor-butterfly), so every launch shape gives BIT-identical sums -- which is
     what lets small multi-GPU shares use more lanes per pixel than a full frame and still reproduce it exactly."""
     W, H, pp = 100, 70, 6
-    monkeypatch.setenv("PT_SAMPLE_LANES_LOG2", str(lanes))
     rc = render.RenderCore(0)
+    rc.set_tuning(sample_lanes_log2=lanes)
     rc.upload_scene(worlds(5).scene(W, H))
     rc.render(W, H, pp, seed=2)
     _, a, _ = rc.readback(False, True)
-    monkeypatch.delenv("PT_SAMPLE_LANES_LOG2")
     rc2 = render.RenderCore(0)
     rc2.upload_scene(worlds(5).scene(W, H))
     rc2.render(W, H, pp, seed=2)
@@ -129,7 +128,7 @@ def test_wavefront_kernel_renders_the_same_samples(worlds, w, lens):
 
 
 @pytest.mark.parametrize("w,lens", [(5, False), (5, True), (2, False), (4, False)])
-def test_cooperative_sparse_walks_do_not_change_the_samples(worlds, w, lens, monkeypatch):
+def test_cooperative_sparse_walks_do_not_change_the_samples(worlds, w, lens):
     """The PT_F_COOP kernel family traces the walks that few lanes of a warp enter one ray at a time with all 32
     lanes over the cluster cut of the tree (pt_cluster.h, pt_coop_trace): the same candidates, the same
     (t, id) minimum -- bit-identical sums and ray counts for any threshold, on triangle and sphere trees.
@@ -137,12 +136,9 @@ def test_cooperative_sparse_walks_do_not_change_the_samples(worlds, w, lens, mon
     W, H, pp = 200, 120, 5
     sc = worlds(w).scene(W, H, lens=lens)
     res = []
-    for coop in ("0", None, "1", "5", "32"):            # off, the default (12 for triangles, off for spheres), thresholds
-        if coop is None:
-            monkeypatch.delenv("PT_COOP_MAX", raising=False)
-        else:
-            monkeypatch.setenv("PT_COOP_MAX", coop)
-        rc = render.RenderCore(0)                        # the environment is read by pt_create
+    for coop in (0, -1, 1, 5, 32):            # off, the default (12 for triangles, off for spheres), thresholds
+        rc = render.RenderCore(0)
+        rc.set_tuning(coop_max=coop)                     # before the upload: the cluster cut is built there
         rc.upload_scene(sc)
         rc.render(W, H, pp, seed=11)
         _, a, st = rc.readback(False, True)
@@ -154,22 +150,18 @@ def test_cooperative_sparse_walks_do_not_change_the_samples(worlds, w, lens, mon
 
 
 @pytest.mark.parametrize("batch", [1, 8, 32])
-def test_shade_deferral_does_not_change_the_samples(worlds, batch, monkeypatch):
+def test_shade_deferral_does_not_change_the_samples(worlds, batch):
     """Parking lanes until `shade_batch` of them need a BRDF sample is scheduling only: bit-identical sums."""
     W, H, pp = 120, 80, 6
     res = []
-    for b in (None, batch):
-        if b is None:
-            monkeypatch.delenv("PT_SHADE_BATCH", raising=False)
-        else:
-            monkeypatch.setenv("PT_SHADE_BATCH", str(b))
+    for b in (0, batch):
         for w in (1, 5):
             rc = render.RenderCore(0)
+            rc.set_tuning(shade_batch=b)
             rc.upload_scene(worlds(w).scene(W, H))
             rc.render(W, H, pp, seed=4)
             res.append(rc.readback(False, True)[1])
             rc.close()
-    monkeypatch.delenv("PT_SHADE_BATCH", raising=False)
     assert np.array_equal(res[0], res[2]) and np.array_equal(res[1], res[3])
 
 @pytest.mark.parametrize("w,W,H", [(2, 320, 180), (4, 320, 180), (5, 480, 270)])
@@ -332,3 +324,201 @@ def test_headline_config_properties(core, worlds):
         _, ar, _ = _frame(core, W, H, pp, seed=1, tile_rank=r, tile_count=8)
         mine = ar[..., 3] > 0
         assert np.array_equal(ar[mine], a[mine]) and abs(mine.mean() - 1 / 8) < 0.01
+
+
+def test_resolve_pack_and_one_kernel_unpack_equal_the_full_frame(core, worlds):
+    """The multi-GPU tile exchange as it runs now: every rank resolves ITS tiles straight into the tile-major pack
+    (pt_resolve_pack_tiles), the packs sit back to back in one gathered buffer, and one kernel scatters all of them
+    (pt_unpack_gathered).  Byte-identical to the unsharded frame; also to the host mirror used by the gloo tests."""
+    import torch
+    from pathtracer_b200 import dist as D
+    W, H, pp, G = 300, 170, 3, 3
+    core.upload_scene(worlds(5).scene(W, H))
+    full_b, _, _ = _frame(core, W, H, pp, seed=9)
+    n_max = D.max_tiles_per_rank(W, H, G) * 1024
+    gathered = torch.zeros((G, n_max), dtype=torch.int32, device="cuda")
+    for r in range(G):
+        core.render(W, H, pp, seed=9, tile_rank=r, tile_count=G)
+        n = core.resolve_pack_tiles(gathered[r].data_ptr(), r, G)
+        assert n == len(D.my_tiles(W, H, r, G))
+        core.synchronize()
+    core.render(W, H, 0, seed=9)                       # empty accumulator: the frame must come from the packs alone
+    core.unpack_gathered(gathered.data_ptr(), G, n_max)
+    b, _, _ = core.readback(True, False)               # marked resolved: readback must not resolve the empty accumulator
+    assert np.array_equal(b, full_b)
+    host = D.unpack_gathered_host(gathered.cpu().numpy().view(np.uint32), W, H, G)
+    assert np.array_equal(host, full_b)
+    with pytest.raises(render.PtError):
+        core.unpack_gathered(gathered.data_ptr(), G, 1024)      # stride shorter than a rank's pack
+
+
+def test_resolve_range_matches_resolve(core, worlds):
+    """pt_resolve_range (a rank's share of the pixels after the reduce-scatter) is the same arithmetic as pt_resolve."""
+    import torch
+    W, H, pp = 160, 90, 4
+    core.upload_scene(worlds(3).scene(W, H))
+    b, a, _ = _frame(core, W, H, pp, seed=2)
+    adev, _ = core.device_buffers()
+    acc = torch.as_tensor(adev, device="cuda").view(-1).clone()
+    out = torch.zeros(W * H, dtype=torch.int32, device="cuda")
+    lo, hi = 1000, 9000
+    core.resolve_range(acc[lo * 4:].data_ptr(), out[lo:].data_ptr(), hi - lo)
+    core.synchronize()
+    got = out.cpu().numpy().view(np.uint32)
+    assert np.array_equal(got[lo:hi], b.reshape(-1)[lo:hi]) and (got[:lo] == 0).all() and (got[hi:] == 0).all()
+
+
+def test_keep_textures_flag_skips_the_texel_upload_only(worlds):
+    """PT_SCENE_KEEP_TEXTURES: same (pointer, width, height) as the previous upload -> the device texels are kept
+    (pt_stats.texture_bytes_uploaded == 0) and the image is bit-identical; without the flag everything is re-sent."""
+    W, H, pp = 96, 54, 3
+    sc = worlds(1).scene(W, H)
+    rc = render.RenderCore(0)
+    rc.upload_scene(sc)
+    rc.render(W, H, pp, seed=3)
+    b0, a0, st0 = rc.readback(True, True)
+    tex_bytes = sum(sc.textures[i].width * sc.textures[i].height * 4 for i in range(4) if sc.textures[i].rgba8)
+    assert st0.texture_bytes_uploaded == tex_bytes > 0
+    keep = T.Scene.from_buffer_copy(sc)
+    keep.flags |= T.SCENE_KEEP_TEXTURES
+    rc.upload_scene(keep)
+    rc.render(W, H, pp, seed=3)
+    b1, a1, st1 = rc.readback(True, True)
+    assert st1.texture_bytes_uploaded == 0 and np.array_equal(a0, a1) and np.array_equal(b0, b1)
+    rc.upload_scene(sc)                                 # no flag: sent again
+    rc.render(W, H, pp, seed=3)
+    _, a2, st2 = rc.readback(False, True)
+    assert st2.texture_bytes_uploaded == tex_bytes and np.array_equal(a0, a2)
+    # a different scene in between, then the textured one again with the flag: the slots' sizes still match, the pointers do too
+    rc.upload_scene(worlds(3).scene(W, H))
+    rc.upload_scene(keep)
+    rc.render(W, H, pp, seed=3)
+    _, a3, st3 = rc.readback(False, True)
+    assert np.array_equal(a0, a3)
+    rc.close()
+
+
+def test_scene_reupload_is_stable(worlds):
+    """The scene arena (one pinned staging buffer, one device buffer, one copy) is reused and grown across uploads:
+    small scene -> large scene -> small scene gives the same images as fresh contexts."""
+    W, H, pp = 80, 48, 3
+    fresh = {}
+    for w in (3, 5, 4):
+        rc = render.RenderCore(0)
+        rc.upload_scene(worlds(w).scene(W, H))
+        rc.render(W, H, pp, seed=6)
+        fresh[w] = rc.readback(False, True)[1].copy()
+        rc.close()
+    rc = render.RenderCore(0)
+    for w in (3, 5, 4, 3, 5):
+        rc.upload_scene(worlds(w).scene(W, H))
+        rc.render(W, H, pp, seed=6)
+        assert np.array_equal(rc.readback(False, True)[1], fresh[w]), w
+    rc.close()
+
+
+def test_tuning_is_validated_and_the_library_reads_no_environment(worlds, monkeypatch):
+    L = render.lib()
+    rc = render.RenderCore(0)
+    t = T.Tuning(C.sizeof(T.Tuning), -1, 0, -1, 0, 0, -1, 0)
+    assert L.pt_set_tuning(rc._h, C.byref(t)) == 0
+    for field, bad in [("sample_lanes_log2", 6), ("shade_batch", 33), ("coop_max", 40), ("tri_leaf", 65), ("wf_pixels_log2", 11)]:
+        u = T.Tuning.from_buffer_copy(t)
+        setattr(u, field, bad)
+        assert L.pt_set_tuning(rc._h, C.byref(u)) == -1, field
+    t.struct_size = 8
+    assert L.pt_set_tuning(rc._h, C.byref(t)) == -1
+    cfg = T.Config(4, 0, 0, 0, None)
+    h = C.c_void_p()
+    assert L.pt_create(C.byref(cfg), C.byref(h)) == -1 and b"struct_size" in L.pt_last_error(None)
+    rc.close()
+    # an environment variable that the round-1 library obeyed must change nothing: same kernel, same launch shape
+    W, H, pp = 64, 40, 3
+    out = []
+    for env in (None, "wavefront"):
+        if env:
+            monkeypatch.setenv("PT_KERNEL", env)
+            monkeypatch.setenv("PT_SAMPLE_LANES_LOG2", "0")
+        rc = render.RenderCore(0)
+        rc.upload_scene(worlds(5).scene(W, H))
+        rc.render(W, H, pp, seed=1)
+        out.append(rc.readback(False, True))
+        rc.close()
+    assert np.array_equal(out[0][1], out[1][1]) and out[0][2].kernel_launches == out[1][2].kernel_launches == 1
+
+
+def test_exported_frame_keeps_its_size(worlds):
+    """pt_frame_ipc_handle hands the BGRA frame to other processes: re-allocating it afterwards would leave them with a
+    dangling mapping, so a render at another size is refused; a foreign pointer is refused as a resolve destination."""
+    rc = render.RenderCore(0)
+    rc.upload_scene(worlds(3).scene(64, 32))
+    blob = rc.frame_ipc_handle(64, 32)
+    assert len(blob) == render.IPC_HANDLE_BYTES and int.from_bytes(blob[72:76], "little") == 64 and int.from_bytes(blob[76:80], "little") == 32
+    rc.render(64, 32, 2, seed=1)
+    with pytest.raises(render.PtError) as e:
+        rc.render(32, 32, 2, seed=1)
+    assert e.value.code == -1 and "exported" in str(e.value)
+    _, bdev = rc.device_buffers()
+    with pytest.raises(render.PtError):
+        rc.resolve_tiles_to(bdev.__cuda_array_interface__["data"][0], 0, 1)     # not a mapped peer frame
+    rc.resolve_tiles_to(None, 0, 1)
+    b, _, _ = rc.readback(True, False)
+    rc.render(64, 32, 2, seed=1)
+    assert np.array_equal(rc.readback(True, False)[0], b)
+    rc.close()
+
+
+def _p2p_worker(rank, world, port, out_dir):
+    import os, sys
+    import torch
+    import torch.distributed as dist
+    from conftest import ROOT
+    sys.path.insert(0, ROOT)
+    from pathtracer_b200 import dist as D
+    from pathtracer_b200 import host
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+    core = render.RenderCore(rank, stream=stream.cuda_stream)
+    W, H, pp = 300, 170, 3
+    core.upload_scene(host.HostWorld(5, scene_seed=7).scene(W, H))
+    res = {}
+    for mode in ("tiles", "tiles_p2p", "samples"):
+        fr = D.ShardedFrame(core, W, H, mode)
+        for seed in (4, 5):                              # two frames: the second exercises the frame-reuse ordering
+            out = fr.render(pp, seed=seed)
+            torch.cuda.synchronize()
+            if rank == 0:
+                res[f"{mode}_{seed}"] = out.cpu().numpy().view(np.uint32).copy()
+        dist.barrier()
+        fr.close()
+    if rank == 0:
+        np.savez(os.path.join(out_dir, "frames.npz"), **res)
+    dist.barrier()
+    core.close()
+    dist.destroy_process_group()
+
+
+def test_two_gpu_exchanges_give_the_one_gpu_frame(tmp_path, worlds):
+    """2 ranks over NCCL on 2 GPUs: the gathered tiles, the tiles stored straight into rank 0's frame over NVLink peer
+    memory (tiles_p2p) and the reduce-scatter of sample ranges all reproduce the 1-GPU frame (tiles: bit for bit)."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    import socket
+    import torch.multiprocessing as mp
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    mp.spawn(_p2p_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    got = np.load(tmp_path / "frames.npz")
+    W, H, pp = 300, 170, 3
+    rc = render.RenderCore(0)
+    rc.upload_scene(worlds(5).scene(W, H))
+    for seed in (4, 5):
+        rc.render(W, H, pp, seed=seed)
+        b, _, _ = rc.readback(True, False)
+        assert np.array_equal(got[f"tiles_{seed}"], b)
+        assert np.array_equal(got[f"tiles_p2p_{seed}"], b)
+        assert (got[f"samples_{seed}"] == b).mean() > 0.999
+    rc.close()

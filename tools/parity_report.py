@@ -1,0 +1,133 @@
+#!/usr/bin/env python
+"""Config-size image parity: the reference's own render against this renderer, through the repo's image_compare.
+
+For each BASELINE.json configuration (C1..C5 and the headline 1080p frame): the reference (oracle/_ref, every host core,
+oracle/ref_parallel.py) renders the frame twice with different mt19937 seeds (A, B), the GPU renders it at the SAME
+resolution and spp, and bin/image_compare reports
+    * legacy "Percentage Similarity" and RMSE of the 8-bit images:  reference A vs GPU,  next to  A vs B (the noise floor),
+    * the per-pixel z-test of the HDR means against the sample standard errors:  fraction of |z| > 3, mean z, global z,
+      reference A vs GPU (mean of K GPU renders with different seeds)  next to  A vs B.
+Where the reference at the configuration's spp would take longer than --budget seconds of CPU per render, the largest
+-p that fits is used FOR BOTH SIDES and stated.  Test/measurement infrastructure: runs on a GPU box.
+
+    python tools/parity_report.py [--configs C1,C2,...] [--budget 45] [--k 16] [--out gpurun_out/parity]
+"""
+import argparse, json, os, re, subprocess, sys, time
+import numpy as np
+ROOT = os.path.abspath(os.path.join(os.path.dirname(__file__), ".."))
+sys.path.insert(0, ROOT)
+
+CONFIGS = {   # name: (world, W, H, pp of the configuration, thin lens)
+    "C1": (1, 1280, 720, 16, False), "C2": (2, 1280, 720, 16, False), "C3": (3, 1280, 720, 32, False),
+    "C4": (4, 1920, 1080, 23, True), "C5": (5, 3840, 2160, 32, False), "HEAD": (5, 1920, 1080, 32, False)}
+
+
+def write_hdr(path, mean_sum, count, var_of_mean):
+    H, W, _ = mean_sum.shape
+    a = np.zeros((H, W, 4), np.float32)
+    a[..., :3] = mean_sum
+    a[..., 3] = count
+    v = np.zeros((H, W, 4), np.float32)
+    v[..., :3] = var_of_mean
+    with open(path, "wb") as f:
+        f.write(np.array([W, H], np.int32).tobytes()); f.write(a.tobytes()); f.write(v.tobytes())
+
+
+def image_compare(*args):
+    exe = os.path.join(ROOT, "pathtracer_b200", "bin", "image_compare")
+    return subprocess.run([exe, *args], capture_output=True, text=True, check=True).stdout
+
+
+def parse_ldr(txt):
+    return dict(similarity=float(re.search(r"Percentage Similarity: ([\d.]+)", txt).group(1)),
+                rmse=float(re.search(r"RMSE \(0-255, RGB\): ([\d.]+)", txt).group(1)))
+
+
+def parse_hdr(txt):
+    m = re.search(r"\|z\| > [\d.]+ on ([\d.]+) % .*mean z: (-?[\d.]+)\s+rms z: ([\d.]+)\s+global z of the image mean: (-?[\d.]+)", txt)
+    return dict(frac_z3=float(m.group(1)), mean_z=float(m.group(2)), rms_z=float(m.group(3)), global_z=float(m.group(4)),
+                hdr_rmse=float(re.search(r"HDR RMSE: ([\d.]+)", txt).group(1)))
+
+
+def run_config(name, budget, K, out_dir, rc_cache):
+    from oracle import ref_parallel as RP
+    from pathtracer_b200 import host, render
+    world, W, H, pp_cfg, lens = CONFIGS[name]
+    flags = 1 if lens else 0
+    # probe the reference's rate at -p2 on a quarter-size frame, then take the largest -p that fits the budget
+    t = RP.render(world, W // 4, H // 4, 2, flags, 7, 99)
+    rate = (W // 4) * (H // 4) * 4 / t["seconds"]
+    pp = max(2, min(pp_cfg, int((budget * rate / (W * H)) ** 0.5)))
+    A = RP.render(world, W, H, pp, flags, 7, 1)
+    B = RP.render(world, W, H, pp, flags, 7, 2)
+    spp = pp * pp
+    rc = rc_cache.setdefault("rc", render.RenderCore(0))
+    hw = host.HostWorld(world, scene_seed=7)
+    rc.upload_scene(hw.scene(W, H, lens=lens))
+    acc = np.zeros((H, W, 3), np.float64)
+    acc2 = np.zeros((H, W, 3), np.float64)
+    bgra1, ms = None, []
+    for k in range(K):
+        rc.render(W, H, pp, seed=1 + k)
+        b, a, st = rc.readback(k == 0, True)
+        if k == 0:
+            bgra1 = b.copy()
+        assert (a[..., 3] == spp).all()
+        m = a[..., :3].astype(np.float64) / spp
+        acc += m; acc2 += m * m
+        ms.append(st.render_ms)
+    gm = acc / K
+    gvar_of_kmean = np.maximum(0.0, acc2 / K - gm * gm) / max(1, K - 1)
+    d = os.path.join(out_dir, name)
+    os.makedirs(d, exist_ok=True)
+    host.write_bmp(os.path.join(d, "ref_a.bmp"), A["ldr"]); host.write_bmp(os.path.join(d, "ref_b.bmp"), B["ldr"])
+    host.write_bmp(os.path.join(d, "gpu.bmp"), bgra1)
+    write_hdr(os.path.join(d, "ref_a.hdr.bin"), A["sum"], spp, RP.variance_of_mean(A))
+    write_hdr(os.path.join(d, "ref_b.hdr.bin"), B["sum"], spp, RP.variance_of_mean(B))
+    write_hdr(os.path.join(d, "gpu_k.hdr.bin"), gm * (K * spp), K * spp, gvar_of_kmean)
+    raw = {"ldr_ref_gpu": image_compare(os.path.join(d, "ref_a.bmp"), os.path.join(d, "gpu.bmp")),
+           "ldr_ref_ref": image_compare(os.path.join(d, "ref_a.bmp"), os.path.join(d, "ref_b.bmp")),
+           "hdr_ref_gpu": image_compare("--hdr", os.path.join(d, "ref_a.hdr.bin"), os.path.join(d, "gpu_k.hdr.bin")),
+           "hdr_ref_ref": image_compare("--hdr", os.path.join(d, "ref_a.hdr.bin"), os.path.join(d, "ref_b.hdr.bin"))}
+    for f in ("ref_a.hdr.bin", "ref_b.hdr.bin", "gpu_k.hdr.bin", "ref_b.bmp"):
+        os.remove(os.path.join(d, f))                # the dumps are large; the numbers and two BMPs stay
+    if W * H > 1280 * 720:
+        for f in ("ref_a.bmp", "gpu.bmp"):
+            os.remove(os.path.join(d, f))
+    open(os.path.join(d, "image_compare.txt"), "w").write("\n".join(f"== {k}\n{v}" for k, v in raw.items()))
+    row = dict(config=name, world=world, width=W, height=H, pp_config=pp_cfg, pp_compared=pp, spp_compared=spp, lens=lens,
+               reference_kind=A["kind"], reference_seconds=[A["seconds"], B["seconds"]], host_workers=A["workers"],
+               gpu_renders=K, gpu_ms_per_render=float(np.median(ms)),
+               ref_vs_gpu=dict(**parse_ldr(raw["ldr_ref_gpu"]), **parse_hdr(raw["hdr_ref_gpu"])),
+               ref_vs_ref=dict(**parse_ldr(raw["ldr_ref_ref"]), **parse_hdr(raw["hdr_ref_ref"])))
+    return row
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--configs", default="C1,C2,C3,C4,C5,HEAD")
+    ap.add_argument("--budget", type=float, default=45.0, help="seconds of wall time per reference render")
+    ap.add_argument("--k", type=int, default=16)
+    ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "parity"))
+    a = ap.parse_args()
+    os.makedirs(a.out, exist_ok=True)
+    rows, cache = [], {}
+    for name in a.configs.split(","):
+        t0 = time.time()
+        row = run_config(name, a.budget, a.k, a.out, cache)
+        row["seconds_total"] = time.time() - t0
+        rows.append(row)
+        print(json.dumps(row), flush=True)
+        json.dump(rows, open(os.path.join(a.out, "parity_report.json"), "w"), indent=1)
+    md = ["| Config | compared at | pair | Percentage Similarity | RMSE (0-255) | HDR RMSE | \\|z\\| > 3 | mean z | global z |", "|---|---|---|---|---|---|---|---|---|"]
+    for r in rows:
+        for pair, k in (("reference vs GPU", "ref_vs_gpu"), ("reference vs reference (noise floor)", "ref_vs_ref")):
+            v = r[k]
+            md.append(f"| {r['config']} w{r['world']} {r['width']}x{r['height']}{' -d' if r['lens'] else ''} | -p{r['pp_compared']} ({r['spp_compared']} spp; config -p{r['pp_config']}) | {pair} | "
+                      f"{v['similarity']:.4f} % | {v['rmse']:.4f} | {v['hdr_rmse']:.5f} | {v['frac_z3']:.3f} % | {v['mean_z']:+.4f} | {v['global_z']:+.2f} |")
+    open(os.path.join(a.out, "parity_report.md"), "w").write("\n".join(md) + "\n")
+    print("\n".join(md))
+
+
+if __name__ == "__main__":
+    main()
