@@ -111,27 +111,19 @@ __device__ __forceinline__ float dot3(float4 a, float3 b) { return a.x * b.x + a
 __device__ __forceinline__ float3 cross3(float3 a, float3 b) {
     return f3(a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y);
 }
-// Fast divide and reciprocal square root.  Default: the CUDA intrinsics (a MUFU plus range handling: |y| > 2^126 for the
-// divide, denormal arguments for the rsqrt -- cases this path never produces).  -DPT_X_BARE_MUFU (experiment build,
-// tools/r02_experiments.sh) issues the bare MUFU.RCP / MUFU.RSQ instead: same values on the normal range, ~5 instructions
-// fewer per call; to be adopted only if tools/ab_identity.py shows every output bit-identical.
+// Fast divide and reciprocal square root: the bare MUFU.RCP / MUFU.RSQ.  The CUDA intrinsics (__fdividef, rsqrtf) wrap the
+// same MUFU in range handling (|y| > 2^126 for the divide, denormal arguments for the rsqrt) -- cases this path never
+// produces -- at ~5 instructions per call, 80 instructions of k_render<624>.  Same values on the normal range: every output
+// array bit-identical, +0.6 ... +2.2 % per world (tools/ab_identity.py, profiles/r02a_ab_compare_old_accl_mufu.json).
 __device__ __forceinline__ float pt_fdiv(float x, float y) {
-#ifdef PT_X_BARE_MUFU
     float r;
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(y));
     return x * r;
-#else
-    return __fdividef(x, y);
-#endif
 }
 __device__ __forceinline__ float pt_rsqrt(float x) {
-#ifdef PT_X_BARE_MUFU
     float r;
     asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
     return r;
-#else
-    return rsqrtf(x);
-#endif
 }
 __device__ __forceinline__ float3 normalize3(float3 a) {
     float inv = pt_rsqrt(dot3(a, a));
@@ -197,5 +189,6 @@ enum : uint32_t {
     PT_F_ALL = 63u | 128u,
     PT_F_DEFER = 64u,     // kernel policy, not a scene feature: park lanes that need a BRDF sample (pt_kernels.cuh)
     PT_F_COOP = 512u,     // kernel policy: sparse BVH walks (few lanes of the warp) are traced one ray at a time by all 32 lanes
+    PT_F_RESUME = 1024u,  // kernel policy: resumable per-lane walks that yield when enough lanes hold a finished walk (sphere trees)
     PT_F_LENS = 128u      // thin-lens camera (-d, always in world 4); pinhole-only variants drop that code
 };

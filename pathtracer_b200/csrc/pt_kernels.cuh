@@ -32,6 +32,12 @@ __host__ __device__ constexpr int pt_render_min_blocks(uint32_t F) {
     X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_COOP) X(PT_F_SPH_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_COOP) \
     X(PT_F_SPH_BVH | PT_F_LENS | PT_F_COOP) X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_LENS | PT_F_COOP)
 
+// megakernel only: sphere-tree families with PT_F_RESUME (resumable per-lane walks that yield once `walk_exit` lanes hold a
+// finished walk, so that those lanes shade / regenerate instead of idling behind the longest walk of the warp)
+#define PT_RENDER_RESUME_VARIANTS(X) \
+    X(PT_F_SPH_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_RESUME) X(PT_F_SPH_BVH | PT_F_LENS | PT_F_RESUME) \
+    X(PT_F_SPH_BVH | PT_F_LIGHT | PT_F_LENS | PT_F_DEFER | PT_F_RESUME)
+
 #define PT_N_COUNTERS 4             // [0] rays [1] NaN retries [2] samples dropped after PT_MAX_NAN_RETRIES [3] -
 
 struct PtRenderArgs {
@@ -47,6 +53,7 @@ struct PtRenderArgs {
     float4 *accum;                      // width*height: sum r,g,b + number of samples
     unsigned long long *counters;       // [0] rays, [1] NaN retries, [2] samples
     uint32_t coop_max;                  // PT_F_COOP variants: walks entered by <= coop_max lanes are traced cooperatively
+    uint32_t walk_exit;                 // PT_F_RESUME variants: the walk loop yields when this many lanes hold a finished walk
 };
 
 // ---- camera (RenderTexel's two sampling loops, src/win32_main.cpp:1032-1170) ----------------------
@@ -142,25 +149,17 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
     const PtPixelCam pxc = pt_pixel_cam(A.width, A.height, A.pp, x, y);
     uint32_t retry = 0, n_acc = 0, n_rays = 0, n_nan = 0;
     // Per-pixel sums in a CANONICAL order, whatever the launch shape: sample s belongs to logical lane
-    // (s - s_begin) % 32, a logical lane adds its samples in increasing order, and the 32 partial sums are added in the
-    // order of a 32-lane xor butterfly.  A physical lane owns the 32/S logical lanes sl, sl + S, ...; it works through
-    // them ONE AFTER THE OTHER (samples s, s + 32, s + 64, ... of one logical lane, then the next), so the running sum
-    // lives in three registers and only a finished logical lane is stored (accl: local memory, 32/S stores per pixel
-    // instead of a load + store per sample).  So S = 8 (full frames) and S = 32 (small multi-GPU shares) give
-    // bit-identical pixels.
+    // (s - s_begin) % 32; a physical lane owns 32/S logical lanes and keeps one accumulator for each (local
+    // memory, touched once per finished sample); at the end they are added in the order of a 32-lane xor
+    // butterfly.  So S = 8 (full frames) and S = 32 (small multi-GPU shares) give bit-identical pixels.
+    // (Measured, profiles/r02a_ab_compare_old_accl.json: walking the logical lanes one after the other with the running
+    // sum in three registers -- no load + store per sample -- is bit-identical and 3-5 % SLOWER on every world: four more
+    // live registers at the 64-register cap cost more than the local-memory traffic they remove.)
     const uint32_t n_logical = 32u >> lS;
-    uint32_t k_log = 0;                                    // the logical lane in progress: sl + k_log * S
     uint32_t s = active ? A.s_begin + sl : A.s_end;
-    float3 acc_cur = f3(0, 0, 0);
     float accl[32][3];
 #pragma unroll 1
     for (uint32_t k = 0; k < n_logical; k++) accl[k][0] = accl[k][1] = accl[k][2] = 0.f;
-    // the sample after s in this lane's order; >= s_end when the lane has none left
-    auto next_sample = [&](uint32_t cur, uint32_t k) -> uint32_t {
-        uint32_t n = cur + 32u;
-        if (n >= A.s_end) n = (k + 1u < n_logical) ? A.s_begin + sl + (k + 1u) * Sn : A.s_end;
-        return n;
-    };
     float3 o = f3(0, 0, 0), d = f3(0, 0, 1), beta = f3(1, 1, 1), L = f3(0, 0, 0);
     int depth = 0;
     PtHit h;
@@ -177,10 +176,18 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
     // loses 2 % on w3/w4, whose variants therefore shade at once.  The same deferral for the BVH walk lost everywhere.
     // Scheduling never changes a sample's value: the Philox stream is keyed by (pixel, sample) and every
     // lane adds its own samples in order.
-    enum { NO_RAY = 0, NEW_RAY = 1, NEED_SHADE = 2 };
+    enum { NO_RAY = 0, NEW_RAY = 1, NEED_SHADE = 2, WALKING = 3, HIT_READY = 4 };
     uint32_t state = NO_RAY;
 
     constexpr bool kCoop = (F & PT_F_COOP) && (((F & PT_F_SPH_BVH) != 0) != ((F & PT_F_TRI_BVH) != 0));
+    // PT_F_RESUME (sphere trees: dense but incoherent walks -- camera rays next to bounce rays of every depth -- whose lengths
+    // differ so much inside a warp that the per-lane walk ran at 14 of 32 threads, profiles/r01e_k_render_w{2,4}): the walk
+    // is a resumable state (node, stack pointer, stack) instead of a call.  The warp advances all walking lanes leaf by leaf
+    // and YIELDS as soon as `walk_exit` lanes hold a finished walk; those lanes take their hit, shade, regenerate and
+    // re-enter the tree, then everybody walks on.  Only the schedule changes: same rays, same hits, bit-identical sums.
+    constexpr bool kResume = !kCoop && (F & PT_F_RESUME) && (F & PT_F_SPH_BVH) && !(F & PT_F_TRI_BVH);
+    int w_node = PT_STACK_SENTINEL, w_sp = 1;
+    int w_stack[kResume ? PT_STACK_DEPTH : 1];
 
     while (true) {
         if (state == NO_RAY && s < A.s_end) {
@@ -230,10 +237,58 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
             __syncwarp();
         }
 
+        if (kResume) {
+            PtRayInv rinv;
+            float a = 0.f;
+            if (state == NEW_RAY) {                      // the linear lists, then the walk starts at the root
+                h.t = 3.402823466e+38f;
+                h.id = PT_ID_MISS;
+                a = pt_dot_exact(d);
+                pt_hit_analytic<F>(S, o, d, a, h);
+                w_stack[0] = PT_STACK_SENTINEL;
+                w_sp = 1;
+                w_node = S.sphere_bvh.n_prims ? 0 : PT_STACK_SENTINEL;
+                state = WALKING;
+            }
+            if (state == WALKING) {                      // per-ray constants are cheap to recompute, expensive to keep live
+                a = pt_dot_exact(d);
+                rinv = pt_ray_inv<!(F & PT_F_LENS)>(o, d);
+                if (w_node == PT_STACK_SENTINEL) state = HIT_READY;
+            }
+            const float4 *nodes = reinterpret_cast<const float4 *>(S.sphere_bvh.nodes);
+#pragma unroll 1
+            while (true) {
+                const bool walking = state == WALKING;
+                if (!__any_sync(0xffffffffu, walking)) break;
+                if ((uint32_t)__popc(__ballot_sync(0xffffffffu, state == HIT_READY)) >= A.walk_exit) break;
+                if (walking) {
+                    while (w_node >= 0) {                // descend to the next leaf (nearer child first, culled by the best t)
+                        const float4 b0 = __ldg(nodes + 4 * w_node), b1 = __ldg(nodes + 4 * w_node + 1), b2 = __ldg(nodes + 4 * w_node + 2);
+                        const int4 link = __ldg(reinterpret_cast<const int4 *>(nodes + 4 * w_node + 3));
+                        bool hl, hr;
+                        float ln, rn;
+                        pt_node_slabs(b0, b1, b2, rinv, h.t, hl, hr, ln, rn);
+                        if (hl && hr) {
+                            const bool left_first = ln <= rn;
+                            w_stack[w_sp++] = left_first ? link.y : link.x;
+                            w_node = left_first ? link.x : link.y;
+                        } else if (hl) w_node = link.x;
+                        else if (hr) w_node = link.y;
+                        else w_node = w_stack[--w_sp];
+                    }
+                    if (w_node != PT_STACK_SENTINEL) {
+                        pt_leaf_test<PT_LEAF_SPHERES>(S, w_node, o, d, a, h);
+                        w_node = w_stack[--w_sp];
+                    }
+                    if (w_node == PT_STACK_SENTINEL) state = HIT_READY;
+                }
+            }
+        }
+
         // ---- closest hit, emission, termination rules of RayCast (main.cpp:579-590, 799) ----
         bool done = false;
-        if (state == NEW_RAY) {
-            if (!kCoop) h = pt_closest_hit<F>(S, o, d);
+        if (state == (kResume ? HIT_READY : NEW_RAY)) {
+            if (!kCoop && !kResume) h = pt_closest_hit<F>(S, o, d);
             n_rays++;
             float3 n;
             uint32_t mat;
@@ -246,6 +301,7 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
                 // shade at once, normal and material still in registers (best where most segments continue)
                 if (!done) done = !pt_shade_vertex<F>(S, rng, mat, n, h.t, o, d, beta);
                 depth++;
+                if (kResume) state = NEW_RAY;
             } else {
                 state = NEED_SHADE;
             }
@@ -255,12 +311,10 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
         if (F & PT_F_DEFER) {
             __syncwarp();
             const uint32_t nS = __popc(__ballot_sync(0xffffffffu, state == NEED_SHADE && !done));
-#ifdef PT_X_OLD_ACCL
-            const uint32_t nD = __popc(__ballot_sync(0xffffffffu, done && s + Sn < A.s_end));
-#else
-            const uint32_t nD = __popc(__ballot_sync(0xffffffffu, done && next_sample(s, k_log) < A.s_end));   // lanes that will regenerate
-#endif
-            if (nS >= A.shade_batch || nD == 0) {
+            const uint32_t nD = __popc(__ballot_sync(0xffffffffu, done && s + Sn < A.s_end));   // lanes that will regenerate
+            // shade when the batch is full, or when nobody would trace in the next iteration (no lane regenerates or walks)
+            const bool idle = nD == 0 && !(kResume && __any_sync(0xffffffffu, state == WALKING));
+            if (nS >= A.shade_batch || idle) {
                 if (state == NEED_SHADE && !done) {
                     float3 n;
                     uint32_t mat;
@@ -282,23 +336,12 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
                     L = f3(0, 0, 0);
                     if (A.counters) atomicAdd(A.counters + 2, 1ull);
                 }
-#ifdef PT_X_OLD_ACCL      // A/B switch for one measurement (round-1 order of execution: lane strides by S, sums indexed per sample)
                 const uint32_t kk = ((s - A.s_begin) >> lS) & (n_logical - 1u);
-                accl[kk][0] += L.x; accl[kk][1] += L.y; accl[kk][2] += L.z;
-                n_acc++; s += Sn; retry = 0;
-                continue;
-#endif
-                acc_cur = acc_cur + L;
+                accl[kk][0] += L.x;
+                accl[kk][1] += L.y;
+                accl[kk][2] += L.z;
                 n_acc++;
-                const uint32_t sn = next_sample(s, k_log);
-                if (s + 32u >= A.s_end) {                                   // this logical lane is complete
-                    accl[k_log][0] = acc_cur.x;
-                    accl[k_log][1] = acc_cur.y;
-                    accl[k_log][2] = acc_cur.z;
-                    acc_cur = f3(0, 0, 0);
-                    k_log++;
-                }
-                s = sn;
+                s += Sn;
                 retry = 0;
             }
         }

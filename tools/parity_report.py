@@ -5,8 +5,14 @@ For each BASELINE.json configuration (C1..C5 and the headline 1080p frame): the 
 oracle/ref_parallel.py) renders the frame twice with different mt19937 seeds (A, B), the GPU renders it at the SAME
 resolution and spp, and bin/image_compare reports
     * legacy "Percentage Similarity" and RMSE of the 8-bit images:  reference A vs GPU,  next to  A vs B (the noise floor),
-    * the per-pixel z-test of the HDR means against the sample standard errors:  fraction of |z| > 3, mean z, global z,
-      reference A vs GPU (mean of K GPU renders with different seeds)  next to  A vs B.
+    * the per-pixel z-test of the HDR means against the sample standard error:  fraction of |z| > 3, mean z, global z,
+      reference A vs GPU  next to  A vs B.  The standard error of a pixel's mean at this spp is measured, not assumed: the
+      sample variance of that pixel over K further GPU renders with other seeds (K = 32).  It is used for BOTH pairs, so the
+      two rows are the same statistic on the same scale -- the A-vs-B row, whose rms z must come out near 1, is the check
+      that the reference's estimator has that variance too.  (A pixel's own sum of squares at 16..256 spp is a poor error
+      bar here: the estimator is heavy-tailed -- a 15 W/sr sun times weights 2/pdf -- so the sample variance is correlated
+      with the sample mean and z is skewed even for the reference against itself; both versions are in the raw output.)
+    * a bias test with all the power the GPU can buy: reference A vs the MEAN of the K GPU renders (global z, mean z).
 Where the reference at the configuration's spp would take longer than --budget seconds of CPU per render, the largest
 -p that fits is used FOR BOTH SIDES and stated.  Test/measurement infrastructure: runs on a GPU box.
 
@@ -66,30 +72,33 @@ def run_config(name, budget, K, out_dir, rc_cache):
     rc.upload_scene(hw.scene(W, H, lens=lens))
     acc = np.zeros((H, W, 3), np.float64)
     acc2 = np.zeros((H, W, 3), np.float64)
-    bgra1, ms = None, []
-    for k in range(K):
-        rc.render(W, H, pp, seed=1 + k)
-        b, a, st = rc.readback(k == 0, True)
-        if k == 0:
-            bgra1 = b.copy()
+    ms = []
+    rc.render(W, H, pp, seed=1)                     # THE GPU image of this configuration
+    bgra1, a, _ = rc.readback(True, True)
+    bgra1, g1 = bgra1.copy(), a[..., :3].astype(np.float64) / spp
+    for k in range(K):                              # K more renders: the per-pixel variance of such a mean, and a precise mean
+        rc.render(W, H, pp, seed=1001 + k)
+        _, a, st = rc.readback(False, True)
         assert (a[..., 3] == spp).all()
         m = a[..., :3].astype(np.float64) / spp
         acc += m; acc2 += m * m
         ms.append(st.render_ms)
     gm = acc / K
-    gvar_of_kmean = np.maximum(0.0, acc2 / K - gm * gm) / max(1, K - 1)
+    V = np.maximum(0.0, acc2 / K - gm * gm) * K / max(1, K - 1)          # variance of ONE render's pixel mean
     d = os.path.join(out_dir, name)
     os.makedirs(d, exist_ok=True)
-    host.write_bmp(os.path.join(d, "ref_a.bmp"), A["ldr"]); host.write_bmp(os.path.join(d, "ref_b.bmp"), B["ldr"])
-    host.write_bmp(os.path.join(d, "gpu.bmp"), bgra1)
-    write_hdr(os.path.join(d, "ref_a.hdr.bin"), A["sum"], spp, RP.variance_of_mean(A))
-    write_hdr(os.path.join(d, "ref_b.hdr.bin"), B["sum"], spp, RP.variance_of_mean(B))
-    write_hdr(os.path.join(d, "gpu_k.hdr.bin"), gm * (K * spp), K * spp, gvar_of_kmean)
-    raw = {"ldr_ref_gpu": image_compare(os.path.join(d, "ref_a.bmp"), os.path.join(d, "gpu.bmp")),
-           "ldr_ref_ref": image_compare(os.path.join(d, "ref_a.bmp"), os.path.join(d, "ref_b.bmp")),
-           "hdr_ref_gpu": image_compare("--hdr", os.path.join(d, "ref_a.hdr.bin"), os.path.join(d, "gpu_k.hdr.bin")),
-           "hdr_ref_ref": image_compare("--hdr", os.path.join(d, "ref_a.hdr.bin"), os.path.join(d, "ref_b.hdr.bin"))}
-    for f in ("ref_a.hdr.bin", "ref_b.hdr.bin", "gpu_k.hdr.bin", "ref_b.bmp"):
+    p = lambda f: os.path.join(d, f)
+    host.write_bmp(p("ref_a.bmp"), A["ldr"]); host.write_bmp(p("ref_b.bmp"), B["ldr"]); host.write_bmp(p("gpu.bmp"), bgra1)
+    write_hdr(p("ref_a.hdr.bin"), A["sum"], spp, V); write_hdr(p("ref_b.hdr.bin"), B["sum"], spp, V)
+    write_hdr(p("gpu.hdr.bin"), g1 * spp, spp, V); write_hdr(p("gpu_k.hdr.bin"), gm * (K * spp), K * spp, V / K)
+    write_hdr(p("ref_a_own.hdr.bin"), A["sum"], spp, RP.variance_of_mean(A)); write_hdr(p("ref_b_own.hdr.bin"), B["sum"], spp, RP.variance_of_mean(B))
+    raw = {"ldr_ref_gpu": image_compare(p("ref_a.bmp"), p("gpu.bmp")), "ldr_ref_ref": image_compare(p("ref_a.bmp"), p("ref_b.bmp")),
+           "hdr_ref_gpu": image_compare("--hdr", p("ref_a.hdr.bin"), p("gpu.hdr.bin")),
+           "hdr_ref_ref": image_compare("--hdr", p("ref_a.hdr.bin"), p("ref_b.hdr.bin")),
+           "hdr_ref_gpumean (bias test)": image_compare("--hdr", p("ref_a.hdr.bin"), p("gpu_k.hdr.bin")),
+           "hdr_ref_ref, each side's own sum of squares as the error bar (skewed, see the header of tools/parity_report.py)":
+               image_compare("--hdr", p("ref_a_own.hdr.bin"), p("ref_b_own.hdr.bin"))}
+    for f in ("ref_a.hdr.bin", "ref_b.hdr.bin", "gpu.hdr.bin", "gpu_k.hdr.bin", "ref_a_own.hdr.bin", "ref_b_own.hdr.bin", "ref_b.bmp"):
         os.remove(os.path.join(d, f))                # the dumps are large; the numbers and two BMPs stay
     if W * H > 1280 * 720:
         for f in ("ref_a.bmp", "gpu.bmp"):
@@ -99,6 +108,7 @@ def run_config(name, budget, K, out_dir, rc_cache):
                reference_kind=A["kind"], reference_seconds=[A["seconds"], B["seconds"]], host_workers=A["workers"],
                gpu_renders=K, gpu_ms_per_render=float(np.median(ms)),
                ref_vs_gpu=dict(**parse_ldr(raw["ldr_ref_gpu"]), **parse_hdr(raw["hdr_ref_gpu"])),
+               ref_vs_gpu_mean_of_k={k: v for k, v in parse_hdr(raw["hdr_ref_gpumean (bias test)"]).items() if k in ("mean_z", "global_z")},
                ref_vs_ref=dict(**parse_ldr(raw["ldr_ref_ref"]), **parse_hdr(raw["hdr_ref_ref"])))
     return row
 
@@ -107,7 +117,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--configs", default="C1,C2,C3,C4,C5,HEAD")
     ap.add_argument("--budget", type=float, default=45.0, help="seconds of wall time per reference render")
-    ap.add_argument("--k", type=int, default=16)
+    ap.add_argument("--k", type=int, default=32)
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "parity"))
     a = ap.parse_args()
     os.makedirs(a.out, exist_ok=True)
@@ -119,12 +129,14 @@ def main():
         rows.append(row)
         print(json.dumps(row), flush=True)
         json.dump(rows, open(os.path.join(a.out, "parity_report.json"), "w"), indent=1)
-    md = ["| Config | compared at | pair | Percentage Similarity | RMSE (0-255) | HDR RMSE | \\|z\\| > 3 | mean z | global z |", "|---|---|---|---|---|---|---|---|---|"]
+    md = ["| Config | compared at | pair | Percentage Similarity | RMSE (0-255) | HDR RMSE | \\|z\\| > 3 | mean z | rms z | global z |", "|---|---|---|---|---|---|---|---|---|---|"]
     for r in rows:
         for pair, k in (("reference vs GPU", "ref_vs_gpu"), ("reference vs reference (noise floor)", "ref_vs_ref")):
             v = r[k]
             md.append(f"| {r['config']} w{r['world']} {r['width']}x{r['height']}{' -d' if r['lens'] else ''} | -p{r['pp_compared']} ({r['spp_compared']} spp; config -p{r['pp_config']}) | {pair} | "
-                      f"{v['similarity']:.4f} % | {v['rmse']:.4f} | {v['hdr_rmse']:.5f} | {v['frac_z3']:.3f} % | {v['mean_z']:+.4f} | {v['global_z']:+.2f} |")
+                      f"{v['similarity']:.4f} % | {v['rmse']:.4f} | {v['hdr_rmse']:.5f} | {v['frac_z3']:.3f} % | {v['mean_z']:+.4f} | {v['rms_z']:.3f} | {v['global_z']:+.2f} |")
+        b = r["ref_vs_gpu_mean_of_k"]
+        md.append(f"| | | reference vs mean of {r['gpu_renders']} GPU renders (bias) | | | | | {b['mean_z']:+.4f} | | {b['global_z']:+.2f} |")
     open(os.path.join(a.out, "parity_report.md"), "w").write("\n".join(md) + "\n")
     print("\n".join(md))
 
