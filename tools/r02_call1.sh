@@ -55,7 +55,7 @@ for w in 2 4; do
   for sb in 8 16 24 32; do timeout 60 python tools/profile_render.py --world $w --width 1280 --height 720 --pp 12 --frames 3 --shade-batch $sb --json | tail -1 >> $O/r02a_sweeps.jsonl; done
 done
 # --- config-size parity report
-timeout 1500 python tools/parity_report.py --budget ${BUDGET:-25} --k 16 --out $O/r02b_parity > $O/r02b_parity.log 2>&1
+timeout 1500 python tools/parity_report.py --budget ${BUDGET:-25} --k 32 --out $O/r02b_parity > $O/r02b_parity.log 2>&1
 tail -20 $O/r02b_parity.log
 # --- ncu --set full of the variants that ship (plain run first, as the recipe demands)
 M=smsp__sass_thread_inst_executed_op_fadd_pred_on.sum,smsp__sass_thread_inst_executed_op_fmul_pred_on.sum,smsp__sass_thread_inst_executed_op_ffma_pred_on.sum,smsp__thread_inst_executed.sum
