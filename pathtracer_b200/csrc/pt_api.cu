@@ -263,7 +263,7 @@ static PtPlanar make_planar(const float *A, const float *u, const float *v) {
 }
 
 // the <= 32-cluster cut of a tree for the PT_F_COOP variants; *out stays NULL when the tree has no such cut
-#define PT_WALK_EXIT_DEFAULT 0          // until measured
+static int walk_exit_default(bool triangles) { return triangles ? 0 : 0; }          // until measured
 
 static int coop_threshold(const pt_context *ctx, bool triangles) {
     return ctx->coop_max >= 0 ? ctx->coop_max : (triangles ? 12 : 0);
@@ -314,6 +314,9 @@ static void launch_render(uint32_t features, unsigned blocks, cudaStream_t st, c
     // first variant (listed from specialised to general) whose mask covers the scene's features
 #define X(M) if ((features & ~(uint32_t)(M)) == 0) { k_render<(M)><<<blocks, PT_RENDER_THREADS, 0, st>>>(S, A); return; }
     if (A.coop_max > 0) {          // a family with the warp-cooperative sparse walk, if one covers the scene
+        if (A.walk_exit > 0) {
+            PT_RENDER_COOP_RESUME_VARIANTS(X)
+        }
         PT_RENDER_COOP_VARIANTS(X)
     }
     if (A.walk_exit > 0) {         // a sphere-tree family with resumable walks
@@ -619,8 +622,7 @@ extern "C" int pt_render(pt_context *ctx, const pt_render_params *p) {
             const bool one_tree = (ctx->scene.tri_bvh.n_nodes != 0) != (ctx->scene.sphere_bvh.n_nodes != 0);
             const bool has_cut = ctx->scene.tri_bvh.n_nodes ? ctx->scene.n_tri_clusters != 0 : ctx->scene.n_sph_clusters != 0;
             A.coop_max = (one_tree && has_cut) ? (uint32_t)coop_threshold(ctx, ctx->scene.tri_bvh.n_nodes != 0) : 0u;
-            const bool sphere_tree_only = ctx->scene.sphere_bvh.n_nodes != 0 && ctx->scene.tri_bvh.n_nodes == 0;
-            A.walk_exit = (sphere_tree_only && A.coop_max == 0) ? (uint32_t)(ctx->walk_exit >= 0 ? ctx->walk_exit : PT_WALK_EXIT_DEFAULT) : 0u;
+            A.walk_exit = one_tree ? (uint32_t)(ctx->walk_exit >= 0 ? ctx->walk_exit : walk_exit_default(ctx->scene.tri_bvh.n_nodes != 0)) : 0u;
             uint32_t warps_per_tile = 1024u >> (5u - lS);                  // pixels per tile / pixels per warp
             uint64_t warps = (uint64_t)A.n_my_tiles * warps_per_tile;
             const uint32_t wpb = PT_RENDER_THREADS / 32;

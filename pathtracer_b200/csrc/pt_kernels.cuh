@@ -37,6 +37,9 @@ __host__ __device__ constexpr int pt_render_min_blocks(uint32_t F) {
 #define PT_RENDER_RESUME_VARIANTS(X) \
     X(PT_F_SPH_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_RESUME) X(PT_F_SPH_BVH | PT_F_LENS | PT_F_RESUME) \
     X(PT_F_SPH_BVH | PT_F_LIGHT | PT_F_LENS | PT_F_DEFER | PT_F_RESUME)
+// ... and the cooperative triangle-tree families with resumable dense walks
+#define PT_RENDER_COOP_RESUME_VARIANTS(X) \
+    X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_COOP | PT_F_RESUME) X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_LENS | PT_F_COOP | PT_F_RESUME)
 
 #define PT_N_COUNTERS 4             // [0] rays [1] NaN retries [2] samples dropped after PT_MAX_NAN_RETRIES [3] -
 
@@ -179,13 +182,14 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
     enum { NO_RAY = 0, NEW_RAY = 1, NEED_SHADE = 2, WALKING = 3, HIT_READY = 4 };
     uint32_t state = NO_RAY;
 
-    constexpr bool kCoop = (F & PT_F_COOP) && (((F & PT_F_SPH_BVH) != 0) != ((F & PT_F_TRI_BVH) != 0));
-    // PT_F_RESUME (sphere trees: dense but incoherent walks -- camera rays next to bounce rays of every depth -- whose lengths
+    constexpr bool kOneTree = ((F & PT_F_SPH_BVH) != 0) != ((F & PT_F_TRI_BVH) != 0);
+    constexpr bool kCoop = (F & PT_F_COOP) && kOneTree;
+    // PT_F_RESUME (first built for the sphere trees: dense but incoherent walks -- camera rays next to bounce rays of every depth -- whose lengths
     // differ so much inside a warp that the per-lane walk ran at 14 of 32 threads, profiles/r01e_k_render_w{2,4}): the walk
     // is a resumable state (node, stack pointer, stack) instead of a call.  The warp advances all walking lanes leaf by leaf
     // and YIELDS as soon as `walk_exit` lanes hold a finished walk; those lanes take their hit, shade, regenerate and
     // re-enter the tree, then everybody walks on.  Only the schedule changes: same rays, same hits, bit-identical sums.
-    constexpr bool kResume = !kCoop && (F & PT_F_RESUME) && (F & PT_F_SPH_BVH) && !(F & PT_F_TRI_BVH);
+    constexpr bool kResume = (F & PT_F_RESUME) && kOneTree;
     int w_node = PT_STACK_SENTINEL, w_sp = 1;
     int w_stack[kResume ? PT_STACK_DEPTH : 1];
 
@@ -205,23 +209,33 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
         // PT_F_COOP: every new ray does the linear lists and the root step itself; then the warp votes.  When few lanes
         // enter the tree (bounce rays that cross the mesh's box while their neighbours see sky or ground -- 2/3 of the
         // traversal's warp instructions, profiles/r01e_bvh_walk_occupancy_w5.txt) their rays are traced one after the
-        // other by all 32 lanes over the cluster cut (pt_coop_trace); otherwise each lane walks its own ray as before.
-        if (kCoop) {
+        // other by all 32 lanes over the cluster cut (pt_coop_trace); otherwise each lane walks its own ray.
+        // PT_F_RESUME: that per-lane walk is a resumable state; the warp advances all walking lanes leaf by leaf and yields
+        // once `walk_exit` lanes hold a finished walk.
+        if (kCoop || kResume) {
             constexpr int LEAF = (F & PT_F_TRI_BVH) ? PT_LEAF_TRIS : PT_LEAF_SPHERES;
+            constexpr bool kBareRcp = kCoop || !(F & PT_F_LENS);         // as measured per family (pt_ray_inv)
             const PtBvh &bvh = (F & PT_F_TRI_BVH) ? S.tri_bvh : S.sphere_bvh;
             int node0 = PT_STACK_SENTINEL, far0 = PT_STACK_SENTINEL;
             PtRayInv rinv;
-            if (state == NEW_RAY) {
+            float a = 0.f;
+            const bool fresh = state == NEW_RAY;
+            if (fresh) {
                 h.t = 3.402823466e+38f;
                 h.id = PT_ID_MISS;
-                pt_hit_analytic<F>(S, o, d, pt_dot_exact(d), h);
-                rinv = pt_ray_inv(o, d);
-                pt_bvh_root_step(bvh, rinv, h.t, node0, far0);
+                a = pt_dot_exact(d);
+                pt_hit_analytic<F>(S, o, d, a, h);
+                rinv = pt_ray_inv<kBareRcp>(o, d);
+                if (kCoop) pt_bvh_root_step(bvh, rinv, h.t, node0, far0);
+                else node0 = bvh.n_prims ? 0 : PT_STACK_SENTINEL;
+            } else if (kResume && state == WALKING) {    // per-ray constants are cheap to recompute, expensive to keep live
+                if (LEAF == PT_LEAF_SPHERES) a = pt_dot_exact(d);
+                rinv = pt_ray_inv<kBareRcp>(o, d);
             }
-            __syncwarp();
-            uint32_t m = __ballot_sync(0xffffffffu, node0 != PT_STACK_SENTINEL);
-            if (m != 0u) {
-                if ((uint32_t)__popc(m) <= A.coop_max) {
+            if (kCoop) {
+                __syncwarp();
+                uint32_t m = __ballot_sync(0xffffffffu, node0 != PT_STACK_SENTINEL);
+                if (m != 0u && (uint32_t)__popc(m) <= A.coop_max) {
                     const float4 *cl = (F & PT_F_TRI_BVH) ? S.tri_clusters : S.sph_clusters;
                     const uint32_t ncl = (F & PT_F_TRI_BVH) ? S.n_tri_clusters : S.n_sph_clusters;
 #pragma unroll 1
@@ -230,59 +244,53 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
                         m &= m - 1u;
                         pt_coop_trace<LEAF>(S, cl, ncl, src, lane, o, d, h);
                     }
-                } else if (node0 != PT_STACK_SENTINEL) {
-                    pt_bvh_walk_from<LEAF>(S, bvh, rinv, o, d, pt_dot_exact(d), h, node0, far0);
+                    node0 = PT_STACK_SENTINEL;           // traced
+                } else if (!kResume && node0 != PT_STACK_SENTINEL) {
+                    pt_bvh_walk_from<LEAF>(S, bvh, rinv, o, d, a, h, node0, far0);
+                }
+            }
+            if (kResume) {
+                if (fresh) {
+                    if (node0 != PT_STACK_SENTINEL) {
+                        w_stack[0] = PT_STACK_SENTINEL;
+                        w_sp = 1;
+                        if (far0 != PT_STACK_SENTINEL) w_stack[w_sp++] = far0;
+                        w_node = node0;
+                        state = WALKING;
+                    } else {
+                        state = HIT_READY;
+                    }
+                }
+                const float4 *nodes = reinterpret_cast<const float4 *>(bvh.nodes);
+#pragma unroll 1
+                while (true) {
+                    const bool walking = state == WALKING;
+                    if (!__any_sync(0xffffffffu, walking)) break;
+                    if ((uint32_t)__popc(__ballot_sync(0xffffffffu, state == HIT_READY)) >= A.walk_exit) break;
+                    if (walking) {
+                        while (w_node >= 0) {            // descend to the next leaf (nearer child first, culled by the best t)
+                            const float4 b0 = __ldg(nodes + 4 * w_node), b1 = __ldg(nodes + 4 * w_node + 1), b2 = __ldg(nodes + 4 * w_node + 2);
+                            const int4 link = __ldg(reinterpret_cast<const int4 *>(nodes + 4 * w_node + 3));
+                            bool hl, hr;
+                            float ln, rn;
+                            pt_node_slabs(b0, b1, b2, rinv, h.t, hl, hr, ln, rn);
+                            if (hl && hr) {
+                                const bool left_first = ln <= rn;
+                                w_stack[w_sp++] = left_first ? link.y : link.x;
+                                w_node = left_first ? link.x : link.y;
+                            } else if (hl) w_node = link.x;
+                            else if (hr) w_node = link.y;
+                            else w_node = w_stack[--w_sp];
+                        }
+                        if (w_node != PT_STACK_SENTINEL) {
+                            pt_leaf_test<LEAF>(S, w_node, o, d, a, h);
+                            w_node = w_stack[--w_sp];
+                        }
+                        if (w_node == PT_STACK_SENTINEL) state = HIT_READY;
+                    }
                 }
             }
             __syncwarp();
-        }
-
-        if (kResume) {
-            PtRayInv rinv;
-            float a = 0.f;
-            if (state == NEW_RAY) {                      // the linear lists, then the walk starts at the root
-                h.t = 3.402823466e+38f;
-                h.id = PT_ID_MISS;
-                a = pt_dot_exact(d);
-                pt_hit_analytic<F>(S, o, d, a, h);
-                w_stack[0] = PT_STACK_SENTINEL;
-                w_sp = 1;
-                w_node = S.sphere_bvh.n_prims ? 0 : PT_STACK_SENTINEL;
-                state = WALKING;
-            }
-            if (state == WALKING) {                      // per-ray constants are cheap to recompute, expensive to keep live
-                a = pt_dot_exact(d);
-                rinv = pt_ray_inv<!(F & PT_F_LENS)>(o, d);
-                if (w_node == PT_STACK_SENTINEL) state = HIT_READY;
-            }
-            const float4 *nodes = reinterpret_cast<const float4 *>(S.sphere_bvh.nodes);
-#pragma unroll 1
-            while (true) {
-                const bool walking = state == WALKING;
-                if (!__any_sync(0xffffffffu, walking)) break;
-                if ((uint32_t)__popc(__ballot_sync(0xffffffffu, state == HIT_READY)) >= A.walk_exit) break;
-                if (walking) {
-                    while (w_node >= 0) {                // descend to the next leaf (nearer child first, culled by the best t)
-                        const float4 b0 = __ldg(nodes + 4 * w_node), b1 = __ldg(nodes + 4 * w_node + 1), b2 = __ldg(nodes + 4 * w_node + 2);
-                        const int4 link = __ldg(reinterpret_cast<const int4 *>(nodes + 4 * w_node + 3));
-                        bool hl, hr;
-                        float ln, rn;
-                        pt_node_slabs(b0, b1, b2, rinv, h.t, hl, hr, ln, rn);
-                        if (hl && hr) {
-                            const bool left_first = ln <= rn;
-                            w_stack[w_sp++] = left_first ? link.y : link.x;
-                            w_node = left_first ? link.x : link.y;
-                        } else if (hl) w_node = link.x;
-                        else if (hr) w_node = link.y;
-                        else w_node = w_stack[--w_sp];
-                    }
-                    if (w_node != PT_STACK_SENTINEL) {
-                        pt_leaf_test<PT_LEAF_SPHERES>(S, w_node, o, d, a, h);
-                        w_node = w_stack[--w_sp];
-                    }
-                    if (w_node == PT_STACK_SENTINEL) state = HIT_READY;
-                }
-            }
         }
 
         // ---- closest hit, emission, termination rules of RayCast (main.cpp:579-590, 799) ----

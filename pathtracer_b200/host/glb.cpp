@@ -38,6 +38,8 @@ struct Json {
 struct Parser {
     const char *p, *end;
     bool ok = true;
+    int depth = 0;                    // nesting of arrays / objects; a hostile file must not overflow the C++ stack
+    static constexpr int kMaxDepth = 64;
     void ws() { while (p < end && (*p == ' ' || *p == '\t' || *p == '\n' || *p == '\r')) p++; }
     bool lit(const char *s) { size_t n = std::strlen(s); if ((size_t)(end - p) >= n && !std::memcmp(p, s, n)) { p += n; return true; } return false; }
     Json value() {
@@ -45,9 +47,10 @@ struct Parser {
         ws();
         if (p >= end) { ok = false; return j; }
         char c = *p;
+        if ((c == '{' || c == '[') && ++depth > kMaxDepth) { ok = false; return j; }
         if (c == '{') {
             p++; j.kind = Json::Obj; ws();
-            if (p < end && *p == '}') { p++; return j; }
+            if (p < end && *p == '}') { p++; depth--; return j; }
             while (ok) {
                 ws();
                 Json k = string_value();
@@ -61,9 +64,10 @@ struct Parser {
                 if (p < end && *p == '}') { p++; break; }
                 ok = false;
             }
+            depth--;
         } else if (c == '[') {
             p++; j.kind = Json::Arr; ws();
-            if (p < end && *p == ']') { p++; return j; }
+            if (p < end && *p == ']') { p++; depth--; return j; }
             while (ok) {
                 j.arr.push_back(value());
                 ws();
@@ -71,6 +75,7 @@ struct Parser {
                 if (p < end && *p == ']') { p++; break; }
                 ok = false;
             }
+            depth--;
         } else if (c == '"') {
             j = string_value();
         } else if (lit("true")) { j.kind = Json::Bool; j.b = true; }
@@ -98,7 +103,7 @@ struct Parser {
                     case 'r': j.str += '\r'; break;
                     case 'b': j.str += '\b'; break;
                     case 'f': j.str += '\f'; break;
-                    case 'u': j.str += '?'; p += 4; break;     // names only; not needed for geometry
+                    case 'u': j.str += '?'; p += (end - p > 4) ? 4 : (end - p - 1); break;     // names only; not needed for geometry
                     default: j.str += *p; break;
                 }
                 p++;
@@ -135,20 +140,24 @@ bool resolve_accessor(const Json &root, long index, const std::vector<uint8_t> &
     const Json *bvi = a.get("bufferView");
     if (!bvi) return false;                                      // sparse / zero-filled accessors: not supported
     const Json *views = root.get("bufferViews");
-    if (!views || (size_t)bvi->as_int(-1) >= views->size()) return false;
+    if (!views || bvi->as_int(-1) < 0 || (size_t)bvi->as_int(-1) >= views->size()) return false;
     const Json &v = views->arr[bvi->as_int(0)];
     if (v.get("buffer") && v.get("buffer")->as_int(0) != 0) return false;   // GLB: buffer 0 is the BIN chunk
-    size_t voff = v.get("byteOffset") ? (size_t)v.get("byteOffset")->as_int(0) : 0;
-    size_t aoff = a.get("byteOffset") ? (size_t)a.get("byteOffset")->as_int(0) : 0;
+    // every integer read from the file is range-checked before it becomes a size: a negative or huge value must not wrap
+    auto nonneg = [](const Json *j, long dflt, size_t &out) { long x = j ? j->as_int(dflt) : dflt; if (x < 0) return false; out = (size_t)x; return true; };
+    size_t voff = 0, aoff = 0, bstride = 0;
+    if (!nonneg(v.get("byteOffset"), 0, voff) || !nonneg(a.get("byteOffset"), 0, aoff) || !nonneg(a.get("count"), 0, out.count) ||
+        !nonneg(v.get("byteStride"), 0, bstride))
+        return false;
     out.component = (int)(a.get("componentType") ? a.get("componentType")->as_int(0) : 0);
     out.ncomp = a.get("type") ? type_components(a.get("type")->str) : 0;
-    out.count = a.get("count") ? (size_t)a.get("count")->as_int(0) : 0;
     out.normalized = a.get("normalized") && a.get("normalized")->b;
     size_t elem = (size_t)component_size(out.component) * out.ncomp;
     if (elem == 0) return false;
-    size_t bstride = v.get("byteStride") ? (size_t)v.get("byteStride")->as_int(0) : 0;
     out.stride = bstride ? bstride : elem;
-    if (out.count && voff + aoff + (out.count - 1) * out.stride + elem > bin.size()) return false;
+    if (voff > bin.size() || aoff > bin.size() - voff) return false;
+    const size_t room = bin.size() - voff - aoff;                            // bytes from the first element to the end of BIN
+    if (out.count && (room < elem || (out.count - 1) > (room - elem) / out.stride)) return false;
     out.base = bin.data() + voff + aoff;
     return true;
 }
@@ -224,13 +233,16 @@ bool load_glb(const char *path, std::vector<float> &tri_points, std::vector<int3
         if (const Json *roots = scene.get("nodes"))
             for (auto &n : roots->arr) stack.push_back(n.as_int(-1));
 
+    std::vector<char> visited(nodes->size(), 0);       // a valid glTF node graph is a forest: a cycle or a shared child is an error
     while (!stack.empty()) {
         long ni = stack.back();
         stack.pop_back();
         if (ni < 0 || (size_t)ni >= nodes->size()) { set_error("GLB node index out of range"); return false; }
+        if (visited[ni]) { set_error("GLB node graph is not a forest (a node is reachable twice)"); return false; }
+        visited[ni] = 1;
         const Json &node = nodes->arr[ni];
         const Json *mesh_i = node.get("mesh");
-        if (mesh_i && meshes && (size_t)mesh_i->as_int(-1) < meshes->size()) {
+        if (mesh_i && meshes && mesh_i->as_int(-1) >= 0 && (size_t)mesh_i->as_int(-1) < meshes->size()) {
             const Json *prims = meshes->arr[mesh_i->as_int(0)].get("primitives");
             for (size_t pi = 0; prims && pi < prims->size(); pi++) {
                 const Json &prim = prims->arr[pi];
@@ -239,7 +251,7 @@ bool load_glb(const char *path, std::vector<float> &tri_points, std::vector<int3
 
                 int32_t mat_idx = 1;
                 const Json *pm = prim.get("material");
-                if (pm && mats && (size_t)pm->as_int(-1) < mats->size()) {
+                if (pm && mats && pm->as_int(-1) >= 0 && (size_t)pm->as_int(-1) < mats->size()) {
                     const Json &gm = mats->arr[pm->as_int(0)];
                     if (const Json *pbr = gm.get("pbrMetallicRoughness")) {
                         const Json *bct = pbr->get("baseColorTexture");

@@ -149,9 +149,9 @@ def test_cooperative_sparse_walks_do_not_change_the_samples(worlds, w, lens):
         assert rays == res[0][1] and nan == res[0][2]
 
 
-@pytest.mark.parametrize("w,lens", [(2, False), (4, True), (2, True), (4, False)])
+@pytest.mark.parametrize("w,lens", [(2, False), (4, True), (2, True), (4, False), (5, False), (5, True)])
 def test_resumable_walks_do_not_change_the_samples(worlds, w, lens):
-    """PT_F_RESUME (sphere trees): the per-lane walk is a resumable state and the warp's walk loop yields once `walk_exit`
+    """PT_F_RESUME (sphere trees, and the dense walks of the cooperative triangle-tree kernels): the per-lane walk is a resumable state and the warp's walk loop yields once `walk_exit`
     lanes hold a finished walk, so that they shade and regenerate instead of idling behind the longest walk.  Scheduling
     only: bit-identical sums, ray counts and NaN redraws for every threshold (0 = walks run to completion, the old kernel)."""
     W, H, pp = 200, 120, 5

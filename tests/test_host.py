@@ -154,3 +154,69 @@ def test_args_long_options(capfd):
 def test_args_help(capfd):
     rc, o, out = _parse(["-h"], capfd)
     assert rc == 1 and out.startswith("usage: Pathtracer.exe [options]\n") and "\tw<int>" in out and "5:\tMario N64 model." in out
+
+
+def _glb(json_obj, bin_bytes=b""):
+    import json, struct
+    js = json.dumps(json_obj).encode() if not isinstance(json_obj, bytes) else json_obj
+    js += b" " * (-len(js) % 4)
+    bin_bytes += b"\0" * (-len(bin_bytes) % 4)
+    chunks = struct.pack("<II", len(js), 0x4E4F534A) + js
+    if bin_bytes:
+        chunks += struct.pack("<II", len(bin_bytes), 0x004E4942) + bin_bytes
+    return b"glTF" + struct.pack("<II", 2, 12 + len(chunks)) + chunks
+
+
+def _load_glb(path):
+    import ctypes as C
+    L = host.lib()
+    L.pt_host_load_glb.argtypes = [C.c_char_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_uint32),
+                                   C.POINTER(C.c_void_p), C.POINTER(C.c_uint32), C.c_uint32]
+    pts, mats, nm = C.c_void_p(), C.c_void_p(), C.c_void_p()
+    nt, nn = C.c_uint32(), C.c_uint32()
+    rc = L.pt_host_load_glb(str(path).encode(), C.byref(pts), C.byref(mats), C.byref(nt), C.byref(nm), C.byref(nn), 3)
+    return rc, nt.value
+
+
+def test_glb_parser_rejects_hostile_files(tmp_path):
+    """The GLB reader is written from the specification; a malformed file must fail cleanly -- no out-of-bounds read,
+    no unbounded recursion, no endless walk -- where the reference would hand it to cgltf (main.cpp:1454-1470)."""
+    import struct
+    tri = struct.pack("<9f", 0, 0, 0, 1, 0, 0, 0, 1, 0)
+
+    def doc(**over):
+        d = {"scenes": [{"nodes": [0]}], "nodes": [{"mesh": 0}],
+             "meshes": [{"primitives": [{"attributes": {"POSITION": 0}}]}],
+             "accessors": [{"bufferView": 0, "componentType": 5126, "type": "VEC3", "count": 3}],
+             "bufferViews": [{"buffer": 0, "byteOffset": 0, "byteLength": 36}], "buffers": [{"byteLength": 36}]}
+        for k, v in over.items():
+            d[k] = v
+        return d
+
+    p = tmp_path / "ok.glb"
+    p.write_bytes(_glb(doc(), tri))
+    assert _load_glb(p) == (0, 1)                                           # the well-formed file: one triangle
+    bad = {
+        "negative_view_offset": doc(bufferViews=[{"buffer": 0, "byteOffset": -64}]),
+        "negative_accessor_offset": doc(accessors=[{"bufferView": 0, "byteOffset": -4, "componentType": 5126, "type": "VEC3", "count": 3}]),
+        "negative_count": doc(accessors=[{"bufferView": 0, "componentType": 5126, "type": "VEC3", "count": -3}]),
+        "count_times_stride_wraps": doc(accessors=[{"bufferView": 0, "componentType": 5126, "type": "VEC3", "count": 2 ** 62}],
+                                        bufferViews=[{"buffer": 0, "byteStride": 8}]),
+        "count_past_the_end": doc(accessors=[{"bufferView": 0, "componentType": 5126, "type": "VEC3", "count": 4}]),
+        "offset_past_the_end": doc(bufferViews=[{"buffer": 0, "byteOffset": 40}]),
+        "negative_view_index": doc(accessors=[{"bufferView": -1, "componentType": 5126, "type": "VEC3", "count": 3}]),
+        "cyclic_nodes": doc(nodes=[{"mesh": 0, "children": [1]}, {"children": [0]}]),
+        "shared_child": doc(scenes=[{"nodes": [0, 0]}]),
+    }
+    for name, d in bad.items():
+        q = tmp_path / (name + ".glb")
+        q.write_bytes(_glb(d, tri))
+        rc, _ = _load_glb(q)
+        assert rc != 0, name
+    deep = tmp_path / "deep.glb"
+    deep.write_bytes(_glb(b'{"a":' + b"[" * 100000 + b"]" * 100000 + b"}", tri))
+    assert _load_glb(deep)[0] != 0
+    # negative mesh / material indices are ignored like out-of-range ones (the reference indexes through cgltf pointers)
+    q = tmp_path / "neg_mesh.glb"
+    q.write_bytes(_glb(doc(nodes=[{"mesh": -1}]), tri))
+    assert _load_glb(q) == (0, 0)
