@@ -60,10 +60,11 @@ struct pt_context {
     // scheduling knobs (pt_set_tuning); none of them changes a sample's value
     int sample_lanes_log2 = -1;                // -1 = auto
     bool sah_sweep = true;                     // false: 16-bin SAH everywhere
-    int tri_leaf = 4, sph_leaf = 2;            // max primitives per BVH leaf (measured, profiles/r01f)
+    int tri_leaf = 4, sph_leaf = 3;            // max primitives per BVH leaf (measured, profiles/r01f, r02a_sweeps.jsonl: spheres 3 = +2 % on w2)
     int shade_batch = 0;                       // deferral threshold of k_render (0 = per-variant default)
     // Walks entered by <= coop_max lanes of a warp are traced cooperatively (k_render<... | PT_F_COOP>).  -1 = the measured
-    // default: 12 for a triangle tree (w5 +8.4 %), off for a sphere tree (w2 -0.5 %, w4 +0.6 %; profiles/r01h_coop_check.jsonl).
+    // default: 12 for a triangle tree (w5 +8.4 %, profiles/r01h_coop_check.jsonl), 4 for a sphere tree (w2 +2.1 %, w4 +2.3 %;
+    // 8: +0.6 / +1.9 %, 16 and more lose; profiles/r02a_sweeps.jsonl).
     // pt_tuning.coop_max = n overrides it for both kinds of tree (0 = off).
     int coop_max = -1;
     // PT_F_RESUME variants (sphere trees): the walk loop yields when walk_exit lanes hold a finished walk.  -1 = default.
@@ -266,7 +267,7 @@ static PtPlanar make_planar(const float *A, const float *u, const float *v) {
 static int walk_exit_default(bool triangles) { return triangles ? 0 : 0; }          // until measured
 
 static int coop_threshold(const pt_context *ctx, bool triangles) {
-    return ctx->coop_max >= 0 ? ctx->coop_max : (triangles ? 12 : 0);
+    return ctx->coop_max >= 0 ? ctx->coop_max : (triangles ? 12 : 4);
 }
 
 static int upload_clusters(pt_context *ctx, const ptbvh::Result &r, bool triangles, const float4 **out, uint32_t *n_out) {
@@ -526,7 +527,7 @@ extern "C" int pt_set_tuning(pt_context *ctx, const pt_tuning *t) {
     ctx->coop_max = t->coop_max;
     ctx->walk_exit = t->walk_exit;
     ctx->tri_leaf = t->tri_leaf ? t->tri_leaf : 4;
-    ctx->sph_leaf = t->sph_leaf ? t->sph_leaf : 2;
+    ctx->sph_leaf = t->sph_leaf ? t->sph_leaf : 3;
     ctx->sah_sweep = t->sah_sweep != 0;
     if (t->wf_pixels_log2) ctx->wf.pixels_log2 = t->wf_pixels_log2;
     return PT_OK;

@@ -9,14 +9,14 @@
 #ifndef PT_RENDER_THREADS
 #define PT_RENDER_THREADS 128
 #endif
-// CTAs per SM the register allocation aims at, per variant (measured, profiles/r01d_sweep_occupancy.log):
-// triangles 8 (64 regs, a few spills, +6 %), textures 6 (85 regs), everything else 7 (72 regs).
+// CTAs per SM the register allocation aims at, per variant (measured, profiles/r01d_sweep_occupancy.log, r02a_ab_compare_mb7_on_final.json):
+// triangles 8 (64 regs, a few spills, +6 %; 7 loses 1.1 %), everything else 7 (72 regs; textures: +2.3 % over 6).
 // -DPT_RENDER_MIN_BLOCKS=n overrides it for all variants (tools/build_variants.sh).
 __host__ __device__ constexpr int pt_render_min_blocks(uint32_t F) {
 #ifdef PT_RENDER_MIN_BLOCKS
     return PT_RENDER_MIN_BLOCKS;
 #else
-    return (F & PT_F_TEX) ? 6 : (F & PT_F_TRI_BVH) ? 8 : 7;
+    return (F & PT_F_TRI_BVH) ? 8 : 7;
 #endif
 }
 

@@ -66,7 +66,7 @@ extern "C" void pt_host_print_help(void) {
     std::printf("\nB200 render core additions (long options):\n");
     std::printf("\t--width N --height N          - Frame size (reference: fixed 1280x720 window).\n");
     std::printf("\t--gpus N                      - GPUs of this box to shard the frame over.\n");
-    std::printf("\t--shard tiles|samples         - Interleaved 32x32 tiles (gather) or sample ranges (NCCL reduce).\n");
+    std::printf("\t--shard tiles|samples         - Interleaved 32x32 tiles (peer-copy gather) or sample ranges (peer copy + add of the float sums).\n");
     std::printf("\t--seed N                      - Philox key of the render.\n");
     std::printf("\t--scene-seed N                - mt19937 seed of world 4's sphere layout.\n");
     std::printf("\t--out PATH                    - Output .BMP (default test.bmp).\n");

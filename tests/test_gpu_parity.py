@@ -248,9 +248,10 @@ def test_native_resolution_image_parity_through_image_compare(core, worlds, tmp_
       * RMSE(reference A, GPU) <= 1.1 x RMSE(reference A, reference B): the GPU image is as close to the reference as the
         reference is to itself;
       * per-pixel z = (a - b) / sqrt(2 V), V = the variance of a pixel's mean at this spp MEASURED over 32 further GPU renders:
-        |z| > 3 no more often for (reference, GPU) than for (reference, reference) (x1.5 + 0.2 %), |mean z| < 0.05, and the
-        reference-vs-reference rms z within 15 % of 1 (the reference's estimator has the variance the GPU's has);
-      * no bias: |global z| < 3 for the reference against the MEAN of the 32 GPU renders.
+        |z| > 3 no more often for (reference, GPU) than for (reference, reference) (x1.5 + 0.2 %) and |median z| < 0.05
+        (the estimator is heavy-tailed: mean and rms of z belong to a few firefly pixels, for the reference against itself too);
+      * no bias: |global z| of the whole-image mean < 3 for the reference against the GPU render and against the MEAN of the
+        32 GPU renders, each side with its own variance (the reference's per-pixel sums of squares, the GPU's 32 renders).
     The same comparison at every BASELINE configuration, larger spp: tools/parity_report.py."""
     import sys
     from conftest import ROOT
@@ -281,14 +282,15 @@ def test_native_resolution_image_parity_through_image_compare(core, worlds, tmp_
     P.write_hdr(f("g.hdr"), g1 * spp, spp, V); P.write_hdr(f("gk.hdr"), gm * (K * spp), K * spp, V / K)
     ldr_g, ldr_n = P.parse_ldr(P.image_compare(f("a.bmp"), f("g.bmp"))), P.parse_ldr(P.image_compare(f("a.bmp"), f("b.bmp")))
     hdr_g, hdr_n = P.parse_hdr(P.image_compare("--hdr", f("a.hdr"), f("g.hdr"))), P.parse_hdr(P.image_compare("--hdr", f("a.hdr"), f("b.hdr")))
-    bias = P.parse_hdr(P.image_compare("--hdr", f("a.hdr"), f("gk.hdr")))
-    print(dict(world=w, ldr_ref_gpu=ldr_g, ldr_ref_ref=ldr_n, hdr_ref_gpu=hdr_g, hdr_ref_ref=hdr_n, bias=bias, ref_kind=A["kind"]))
+    P.write_hdr(f("a_own.hdr"), A["sum"], spp, RP.variance_of_mean(A))
+    gz_1 = P.parse_hdr(P.image_compare("--hdr", f("a_own.hdr"), f("g.hdr")))["global_z"]
+    gz_k = P.parse_hdr(P.image_compare("--hdr", f("a_own.hdr"), f("gk.hdr")))["global_z"]
+    print(dict(world=w, ldr_ref_gpu=ldr_g, ldr_ref_ref=ldr_n, hdr_ref_gpu=hdr_g, hdr_ref_ref=hdr_n, global_z=(gz_1, gz_k), ref_kind=A["kind"]))
     assert ldr_g["rmse"] <= 1.1 * ldr_n["rmse"], (ldr_g, ldr_n)
     assert ldr_g["similarity"] >= ldr_n["similarity"] - 0.3, (ldr_g, ldr_n)
-    assert 0.85 < hdr_n["rms_z"] < 1.15, hdr_n
     assert hdr_g["frac_z3"] <= 1.5 * hdr_n["frac_z3"] + 0.2, (hdr_g, hdr_n)
-    assert abs(hdr_g["mean_z"]) < 0.05 and abs(hdr_g["global_z"]) < 3.0, hdr_g
-    assert abs(bias["global_z"]) < 3.0, bias
+    assert abs(hdr_g["median_z"]) < 0.05, hdr_g
+    assert abs(gz_1) < 3.0 and abs(gz_k) < 3.0, (gz_1, gz_k)
 
 
 # ---- isolated taps of the shading helpers -------------------------------------------------
