@@ -144,9 +144,6 @@ typedef struct pt_tuning {
     int32_t  shade_batch;        /* parked lanes before the BRDF code runs, 1..32; 0 = default */
     int32_t  coop_max;           /* walks entered by <= n lanes are traced by the whole warp, 0..32 (0 = never); -1 = default.
                                     The cluster cut is built by pt_upload_scene: set this BEFORE uploading the scene. */
-    int32_t  walk_exit;          /* sphere trees: the per-lane walks of a warp yield when n lanes hold a finished walk, so that those
-                                    lanes shade and regenerate instead of idling behind the longest walk, 1..32 (0 = walks run
-                                    to completion); -1 = default */
     int32_t  tri_leaf, sph_leaf; /* max primitives per BVH leaf, 1..64; 0 = default (4 / 3).  Applies to the next upload. */
     int32_t  sah_sweep;          /* 1 = exact sweep for small nodes (default), 0 = 16-bin SAH everywhere; -1 = default */
     int32_t  wf_pixels_log2;     /* PT_KERNEL_WAVEFRONT: pixels per warp pool; 0 = default */

@@ -84,7 +84,7 @@ class Stats(C.Structure):
 class Tuning(C.Structure):
     _pack_ = 4
     _fields_ = [("struct_size", C.c_uint32), ("sample_lanes_log2", C.c_int32), ("shade_batch", C.c_int32),
-                ("coop_max", C.c_int32), ("walk_exit", C.c_int32), ("tri_leaf", C.c_int32), ("sph_leaf", C.c_int32), ("sah_sweep", C.c_int32),
+                ("coop_max", C.c_int32), ("tri_leaf", C.c_int32), ("sph_leaf", C.c_int32), ("sah_sweep", C.c_int32),
                 ("wf_pixels_log2", C.c_int32)]
 
 

@@ -67,8 +67,6 @@ struct pt_context {
     // 8: +0.6 / +1.9 %, 16 and more lose; profiles/r02a_sweeps.jsonl).
     // pt_tuning.coop_max = n overrides it for both kinds of tree (0 = off).
     int coop_max = -1;
-    // PT_F_RESUME variants (sphere trees): the walk loop yields when walk_exit lanes hold a finished walk.  -1 = default.
-    int walk_exit = -1;
     // single-process multi-GPU (pt_gather_tiles_from / pt_add_accum_from)
     void *pack_buf = nullptr, *stage_buf = nullptr;
     size_t pack_bytes = 0, stage_bytes = 0;
@@ -143,7 +141,6 @@ extern "C" int pt_create(const pt_config *cfg, pt_context **out) {
     if (const char *s = getenv("PT_SAMPLE_LANES_LOG2")) ctx->sample_lanes_log2 = atoi(s);
     if (const char *s = getenv("PT_SHADE_BATCH")) ctx->shade_batch = atoi(s);
     if (const char *s = getenv("PT_COOP_MAX")) ctx->coop_max = std::max(0, std::min(32, atoi(s)));
-    if (const char *s = getenv("PT_WALK_EXIT")) ctx->walk_exit = std::max(0, std::min(32, atoi(s)));
     if (const char *s = getenv("PT_SAH_SWEEP")) ctx->sah_sweep = atoi(s) != 0;
     if (const char *s = getenv("PT_TRI_LEAF")) ctx->tri_leaf = std::max(1, std::min(64, atoi(s)));
     if (const char *s = getenv("PT_SPH_LEAF")) ctx->sph_leaf = std::max(1, std::min(64, atoi(s)));
@@ -264,8 +261,6 @@ static PtPlanar make_planar(const float *A, const float *u, const float *v) {
 }
 
 // the <= 32-cluster cut of a tree for the PT_F_COOP variants; *out stays NULL when the tree has no such cut
-static int walk_exit_default(bool triangles) { return triangles ? 0 : 0; }          // until measured
-
 static int coop_threshold(const pt_context *ctx, bool triangles) {
     return ctx->coop_max >= 0 ? ctx->coop_max : (triangles ? 12 : 4);
 }
@@ -315,13 +310,7 @@ static void launch_render(uint32_t features, unsigned blocks, cudaStream_t st, c
     // first variant (listed from specialised to general) whose mask covers the scene's features
 #define X(M) if ((features & ~(uint32_t)(M)) == 0) { k_render<(M)><<<blocks, PT_RENDER_THREADS, 0, st>>>(S, A); return; }
     if (A.coop_max > 0) {          // a family with the warp-cooperative sparse walk, if one covers the scene
-        if (A.walk_exit > 0) {
-            PT_RENDER_COOP_RESUME_VARIANTS(X)
-        }
         PT_RENDER_COOP_VARIANTS(X)
-    }
-    if (A.walk_exit > 0) {         // a sphere-tree family with resumable walks
-        PT_RENDER_RESUME_VARIANTS(X)
     }
     PT_RENDER_VARIANTS(X)
 #undef X
@@ -519,13 +508,12 @@ extern "C" int pt_set_tuning(pt_context *ctx, const pt_tuning *t) {
     if (!ctx || !t) return PT_ERR_INVALID_ARG;
     if (t->struct_size != sizeof(pt_tuning)) return fail(ctx, PT_ERR_INVALID_ARG, "pt_set_tuning: struct_size mismatch");
     if (t->sample_lanes_log2 < -1 || t->sample_lanes_log2 > 5 || t->shade_batch < 0 || t->shade_batch > 32 || t->coop_max < -1 || t->coop_max > 32 ||
-        t->walk_exit < -1 || t->walk_exit > 32 || t->tri_leaf < 0 || t->tri_leaf > 64 || t->sph_leaf < 0 || t->sph_leaf > 64 || t->sah_sweep < -1 || t->sah_sweep > 1 ||
+        t->tri_leaf < 0 || t->tri_leaf > 64 || t->sph_leaf < 0 || t->sph_leaf > 64 || t->sah_sweep < -1 || t->sah_sweep > 1 ||
         t->wf_pixels_log2 < 0 || t->wf_pixels_log2 > 10)
         return fail(ctx, PT_ERR_INVALID_ARG, "pt_set_tuning: a field is out of range");
     ctx->sample_lanes_log2 = t->sample_lanes_log2;
     ctx->shade_batch = t->shade_batch;
     ctx->coop_max = t->coop_max;
-    ctx->walk_exit = t->walk_exit;
     ctx->tri_leaf = t->tri_leaf ? t->tri_leaf : 4;
     ctx->sph_leaf = t->sph_leaf ? t->sph_leaf : 3;
     ctx->sah_sweep = t->sah_sweep != 0;
@@ -623,7 +611,6 @@ extern "C" int pt_render(pt_context *ctx, const pt_render_params *p) {
             const bool one_tree = (ctx->scene.tri_bvh.n_nodes != 0) != (ctx->scene.sphere_bvh.n_nodes != 0);
             const bool has_cut = ctx->scene.tri_bvh.n_nodes ? ctx->scene.n_tri_clusters != 0 : ctx->scene.n_sph_clusters != 0;
             A.coop_max = (one_tree && has_cut) ? (uint32_t)coop_threshold(ctx, ctx->scene.tri_bvh.n_nodes != 0) : 0u;
-            A.walk_exit = one_tree ? (uint32_t)(ctx->walk_exit >= 0 ? ctx->walk_exit : walk_exit_default(ctx->scene.tri_bvh.n_nodes != 0)) : 0u;
             uint32_t warps_per_tile = 1024u >> (5u - lS);                  // pixels per tile / pixels per warp
             uint64_t warps = (uint64_t)A.n_my_tiles * warps_per_tile;
             const uint32_t wpb = PT_RENDER_THREADS / 32;

@@ -189,6 +189,5 @@ enum : uint32_t {
     PT_F_ALL = 63u | 128u,
     PT_F_DEFER = 64u,     // kernel policy, not a scene feature: park lanes that need a BRDF sample (pt_kernels.cuh)
     PT_F_COOP = 512u,     // kernel policy: sparse BVH walks (few lanes of the warp) are traced one ray at a time by all 32 lanes
-    PT_F_RESUME = 1024u,  // kernel policy: resumable per-lane walks that yield when enough lanes hold a finished walk (sphere trees)
     PT_F_LENS = 128u      // thin-lens camera (-d, always in world 4); pinhole-only variants drop that code
 };

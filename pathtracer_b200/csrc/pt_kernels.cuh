@@ -32,15 +32,6 @@ __host__ __device__ constexpr int pt_render_min_blocks(uint32_t F) {
     X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_COOP) X(PT_F_SPH_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_COOP) \
     X(PT_F_SPH_BVH | PT_F_LENS | PT_F_COOP) X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_LENS | PT_F_COOP)
 
-// megakernel only: sphere-tree families with PT_F_RESUME (resumable per-lane walks that yield once `walk_exit` lanes hold a
-// finished walk, so that those lanes shade / regenerate instead of idling behind the longest walk of the warp)
-#define PT_RENDER_RESUME_VARIANTS(X) \
-    X(PT_F_SPH_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_RESUME) X(PT_F_SPH_BVH | PT_F_LENS | PT_F_RESUME) \
-    X(PT_F_SPH_BVH | PT_F_LIGHT | PT_F_LENS | PT_F_DEFER | PT_F_RESUME)
-// ... and the cooperative triangle-tree families with resumable dense walks
-#define PT_RENDER_COOP_RESUME_VARIANTS(X) \
-    X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_COOP | PT_F_RESUME) X(PT_F_TRI_BVH | PT_F_LIGHT | PT_F_DEFER | PT_F_LENS | PT_F_COOP | PT_F_RESUME)
-
 #define PT_N_COUNTERS 4             // [0] rays [1] NaN retries [2] samples dropped after PT_MAX_NAN_RETRIES [3] -
 
 struct PtRenderArgs {
@@ -56,7 +47,6 @@ struct PtRenderArgs {
     float4 *accum;                      // width*height: sum r,g,b + number of samples
     unsigned long long *counters;       // [0] rays, [1] NaN retries, [2] samples
     uint32_t coop_max;                  // PT_F_COOP variants: walks entered by <= coop_max lanes are traced cooperatively
-    uint32_t walk_exit;                 // PT_F_RESUME variants: the walk loop yields when this many lanes hold a finished walk
 };
 
 // ---- camera (RenderTexel's two sampling loops, src/win32_main.cpp:1032-1170) ----------------------
@@ -179,19 +169,12 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
     // loses 2 % on w3/w4, whose variants therefore shade at once.  The same deferral for the BVH walk lost everywhere.
     // Scheduling never changes a sample's value: the Philox stream is keyed by (pixel, sample) and every
     // lane adds its own samples in order.
-    enum { NO_RAY = 0, NEW_RAY = 1, NEED_SHADE = 2, WALKING = 3, HIT_READY = 4 };
+    enum { NO_RAY = 0, NEW_RAY = 1, NEED_SHADE = 2 };
     uint32_t state = NO_RAY;
 
-    constexpr bool kOneTree = ((F & PT_F_SPH_BVH) != 0) != ((F & PT_F_TRI_BVH) != 0);
-    constexpr bool kCoop = (F & PT_F_COOP) && kOneTree;
-    // PT_F_RESUME (first built for the sphere trees: dense but incoherent walks -- camera rays next to bounce rays of every depth -- whose lengths
-    // differ so much inside a warp that the per-lane walk ran at 14 of 32 threads, profiles/r01e_k_render_w{2,4}): the walk
-    // is a resumable state (node, stack pointer, stack) instead of a call.  The warp advances all walking lanes leaf by leaf
-    // and YIELDS as soon as `walk_exit` lanes hold a finished walk; those lanes take their hit, shade, regenerate and
-    // re-enter the tree, then everybody walks on.  Only the schedule changes: same rays, same hits, bit-identical sums.
-    constexpr bool kResume = (F & PT_F_RESUME) && kOneTree;
-    int w_node = PT_STACK_SENTINEL, w_sp = 1;
-    int w_stack[kResume ? PT_STACK_DEPTH : 1];
+    constexpr bool kCoop = (F & PT_F_COOP) && (((F & PT_F_SPH_BVH) != 0) != ((F & PT_F_TRI_BVH) != 0));
+    // (Resumable per-lane walks that yield to shading / regeneration once some lanes hold a finished walk were built for both
+    // kinds of tree, verified bit-identical and measured slower at every threshold: profiles/r02_rejected_experiments.txt #3.)
 
     while (true) {
         if (state == NO_RAY && s < A.s_end) {
@@ -209,33 +192,25 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
         // PT_F_COOP: every new ray does the linear lists and the root step itself; then the warp votes.  When few lanes
         // enter the tree (bounce rays that cross the mesh's box while their neighbours see sky or ground -- 2/3 of the
         // traversal's warp instructions, profiles/r01e_bvh_walk_occupancy_w5.txt) their rays are traced one after the
-        // other by all 32 lanes over the cluster cut (pt_coop_trace); otherwise each lane walks its own ray.
-        // PT_F_RESUME: that per-lane walk is a resumable state; the warp advances all walking lanes leaf by leaf and yields
-        // once `walk_exit` lanes hold a finished walk.
-        if (kCoop || kResume) {
+        // other by all 32 lanes over the cluster cut (pt_coop_trace); otherwise each lane walks its own ray as before.
+        if (kCoop) {
             constexpr int LEAF = (F & PT_F_TRI_BVH) ? PT_LEAF_TRIS : PT_LEAF_SPHERES;
-            constexpr bool kBareRcp = kCoop || !(F & PT_F_LENS);         // as measured per family (pt_ray_inv)
             const PtBvh &bvh = (F & PT_F_TRI_BVH) ? S.tri_bvh : S.sphere_bvh;
             int node0 = PT_STACK_SENTINEL, far0 = PT_STACK_SENTINEL;
             PtRayInv rinv;
             float a = 0.f;
-            const bool fresh = state == NEW_RAY;
-            if (fresh) {
+            if (state == NEW_RAY) {
                 h.t = 3.402823466e+38f;
                 h.id = PT_ID_MISS;
                 a = pt_dot_exact(d);
                 pt_hit_analytic<F>(S, o, d, a, h);
-                rinv = pt_ray_inv<kBareRcp>(o, d);
-                if (kCoop) pt_bvh_root_step(bvh, rinv, h.t, node0, far0);
-                else node0 = bvh.n_prims ? 0 : PT_STACK_SENTINEL;
-            } else if (kResume && state == WALKING) {    // per-ray constants are cheap to recompute, expensive to keep live
-                if (LEAF == PT_LEAF_SPHERES) a = pt_dot_exact(d);
-                rinv = pt_ray_inv<kBareRcp>(o, d);
+                rinv = pt_ray_inv(o, d);
+                pt_bvh_root_step(bvh, rinv, h.t, node0, far0);
             }
-            if (kCoop) {
-                __syncwarp();
-                uint32_t m = __ballot_sync(0xffffffffu, node0 != PT_STACK_SENTINEL);
-                if (m != 0u && (uint32_t)__popc(m) <= A.coop_max) {
+            __syncwarp();
+            uint32_t m = __ballot_sync(0xffffffffu, node0 != PT_STACK_SENTINEL);
+            if (m != 0u) {
+                if ((uint32_t)__popc(m) <= A.coop_max) {
                     const float4 *cl = (F & PT_F_TRI_BVH) ? S.tri_clusters : S.sph_clusters;
                     const uint32_t ncl = (F & PT_F_TRI_BVH) ? S.n_tri_clusters : S.n_sph_clusters;
 #pragma unroll 1
@@ -244,50 +219,8 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
                         m &= m - 1u;
                         pt_coop_trace<LEAF>(S, cl, ncl, src, lane, o, d, h);
                     }
-                    node0 = PT_STACK_SENTINEL;           // traced
-                } else if (!kResume && node0 != PT_STACK_SENTINEL) {
+                } else if (node0 != PT_STACK_SENTINEL) {
                     pt_bvh_walk_from<LEAF>(S, bvh, rinv, o, d, a, h, node0, far0);
-                }
-            }
-            if (kResume) {
-                if (fresh) {
-                    if (node0 != PT_STACK_SENTINEL) {
-                        w_stack[0] = PT_STACK_SENTINEL;
-                        w_sp = 1;
-                        if (far0 != PT_STACK_SENTINEL) w_stack[w_sp++] = far0;
-                        w_node = node0;
-                        state = WALKING;
-                    } else {
-                        state = HIT_READY;
-                    }
-                }
-                const float4 *nodes = reinterpret_cast<const float4 *>(bvh.nodes);
-#pragma unroll 1
-                while (true) {
-                    const bool walking = state == WALKING;
-                    if (!__any_sync(0xffffffffu, walking)) break;
-                    if ((uint32_t)__popc(__ballot_sync(0xffffffffu, state == HIT_READY)) >= A.walk_exit) break;
-                    if (walking) {
-                        while (w_node >= 0) {            // descend to the next leaf (nearer child first, culled by the best t)
-                            const float4 b0 = __ldg(nodes + 4 * w_node), b1 = __ldg(nodes + 4 * w_node + 1), b2 = __ldg(nodes + 4 * w_node + 2);
-                            const int4 link = __ldg(reinterpret_cast<const int4 *>(nodes + 4 * w_node + 3));
-                            bool hl, hr;
-                            float ln, rn;
-                            pt_node_slabs(b0, b1, b2, rinv, h.t, hl, hr, ln, rn);
-                            if (hl && hr) {
-                                const bool left_first = ln <= rn;
-                                w_stack[w_sp++] = left_first ? link.y : link.x;
-                                w_node = left_first ? link.x : link.y;
-                            } else if (hl) w_node = link.x;
-                            else if (hr) w_node = link.y;
-                            else w_node = w_stack[--w_sp];
-                        }
-                        if (w_node != PT_STACK_SENTINEL) {
-                            pt_leaf_test<LEAF>(S, w_node, o, d, a, h);
-                            w_node = w_stack[--w_sp];
-                        }
-                        if (w_node == PT_STACK_SENTINEL) state = HIT_READY;
-                    }
                 }
             }
             __syncwarp();
@@ -295,8 +228,8 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
 
         // ---- closest hit, emission, termination rules of RayCast (main.cpp:579-590, 799) ----
         bool done = false;
-        if (state == (kResume ? HIT_READY : NEW_RAY)) {
-            if (!kCoop && !kResume) h = pt_closest_hit<F>(S, o, d);
+        if (state == NEW_RAY) {
+            if (!kCoop) h = pt_closest_hit<F>(S, o, d);
             n_rays++;
             float3 n;
             uint32_t mat;
@@ -309,7 +242,6 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
                 // shade at once, normal and material still in registers (best where most segments continue)
                 if (!done) done = !pt_shade_vertex<F>(S, rng, mat, n, h.t, o, d, beta);
                 depth++;
-                if (kResume) state = NEW_RAY;
             } else {
                 state = NEED_SHADE;
             }
@@ -320,9 +252,7 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
             __syncwarp();
             const uint32_t nS = __popc(__ballot_sync(0xffffffffu, state == NEED_SHADE && !done));
             const uint32_t nD = __popc(__ballot_sync(0xffffffffu, done && s + Sn < A.s_end));   // lanes that will regenerate
-            // shade when the batch is full, or when nobody would trace in the next iteration (no lane regenerates or walks)
-            const bool idle = nD == 0 && !(kResume && __any_sync(0xffffffffu, state == WALKING));
-            if (nS >= A.shade_batch || idle) {
+            if (nS >= A.shade_batch || nD == 0) {
                 if (state == NEED_SHADE && !done) {
                     float3 n;
                     uint32_t mat;

@@ -121,10 +121,10 @@ class RenderCore:
     def set_camera(self, cam):
         self._ck(lib().pt_set_camera(self._h, C.byref(cam)))
 
-    def set_tuning(self, sample_lanes_log2=-1, shade_batch=0, coop_max=-1, walk_exit=-1, tri_leaf=0, sph_leaf=0, sah_sweep=-1,
+    def set_tuning(self, sample_lanes_log2=-1, shade_batch=0, coop_max=-1, tri_leaf=0, sph_leaf=0, sah_sweep=-1,
                    wf_pixels_log2=0):
         """Scheduling knobs (pt_tuning): never change a sample.  coop_max / leaf sizes apply to the NEXT upload."""
-        t = T.Tuning(C.sizeof(T.Tuning), sample_lanes_log2, shade_batch, coop_max, walk_exit, tri_leaf, sph_leaf, sah_sweep,
+        t = T.Tuning(C.sizeof(T.Tuning), sample_lanes_log2, shade_batch, coop_max, tri_leaf, sph_leaf, sah_sweep,
                      wf_pixels_log2)
         self._ck(lib().pt_set_tuning(self._h, C.byref(t)))
 

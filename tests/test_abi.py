@@ -45,7 +45,7 @@ def test_struct_sizes_match_header_contract():
     assert C.sizeof(T.Sphere) == 20 and C.sizeof(T.Aabb) == 52 and C.sizeof(T.Camera) == 116
     assert C.sizeof(T.Scene) == 8 * 4 + 7 * 8 + 4 * 16 + 116
     assert T.HIT_DTYPE.itemsize == 28
-    assert C.sizeof(T.Stats) == 56 and C.sizeof(T.Tuning) == 36 and C.sizeof(T.Config) == 24
+    assert C.sizeof(T.Stats) == 56 and C.sizeof(T.Tuning) == 32 and C.sizeof(T.Config) == 24
 
 
 def test_render_core_fails_loudly_without_a_device():

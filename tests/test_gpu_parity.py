@@ -297,7 +297,8 @@ def test_native_resolution_image_parity_through_image_compare(core, worlds, tmp_
 def _one_sphere_scene(material, just_cosine=False, light_emit=15.0):
     """A unit sphere of `material` at the origin under a uniform sky, plus the (required) light sphere: far away and
     black for the no-light cases, overhead and bright otherwise.  Every path is camera -> sphere -> one BRDF sample
-    -> sky / light, so the radiance of a ray IS the BRDF weight of that branch times a constant."""
+    -> sky / light, so the radiance of a ray IS the BRDF weight of that branch times a constant.  (light_emit = 0: the light
+    sphere is an ordinary grey surface that the cone sampler still aims at -- the mixture pdf with a light that adds nothing.)"""
     import ctypes as C
     from pathtracer_b200 import host
     mats = (T.Material * 3)()
@@ -307,7 +308,7 @@ def _one_sphere_scene(material, just_cosine=False, light_emit=15.0):
     mats[1].emit = T.V3(light_emit, light_emit, light_emit)
     for k, v in material.items():
         setattr(mats[2], k, T.V3(*v) if isinstance(v, tuple) else v)
-    sph = (T.Sphere * 2)(T.Sphere(T.V3(0.0, 0.0, 6.0), 1.0 if light_emit else 1e-3, 1), T.Sphere(T.V3(0, 0, 0), 1.0, 2))
+    sph = (T.Sphere * 2)(T.Sphere(T.V3(0.0, 0.0, 6.0), 1.0, 1), T.Sphere(T.V3(0, 0, 0), 1.0, 2))
     s = T.Scene()
     s.struct_size = C.sizeof(T.Scene)
     s.flags = T.SCENE_ALL_MAPS | (T.SCENE_JUST_COSINE if just_cosine else 0)
@@ -329,7 +330,7 @@ _TAPS = [
     ("half metal 0.5 / rough 0.5: both lobes", dict(roughness=0.5, metalness=0.5, metal_color=(0.9, 0.9, 0.2), albedo=(0.2, 0.3, 0.9)), False, 15.0),
     ("pure diffuse with the light: cosine + cone mixture pdf", dict(roughness=1.0, metalness=0.0, albedo=(0.7, 0.7, 0.7)), False, 15.0),
     ("pure diffuse, JUST_COSINE: cosine pdf only", dict(roughness=1.0, metalness=0.0, albedo=(0.7, 0.5, 0.3)), True, 15.0),
-    ("pure diffuse, black far light: light samples contribute nothing", dict(roughness=1.0, metalness=0.0, albedo=(0.3, 0.6, 0.9)), False, 0.0),
+    ("pure diffuse, black light: the cone samples land on a non-emitter", dict(roughness=1.0, metalness=0.0, albedo=(0.3, 0.6, 0.9)), False, 0.0),
 ]
 
 

@@ -149,27 +149,6 @@ def test_cooperative_sparse_walks_do_not_change_the_samples(worlds, w, lens):
         assert rays == res[0][1] and nan == res[0][2]
 
 
-@pytest.mark.parametrize("w,lens", [(2, False), (4, True), (2, True), (4, False), (5, False), (5, True)])
-def test_resumable_walks_do_not_change_the_samples(worlds, w, lens):
-    """PT_F_RESUME (sphere trees, and the dense walks of the cooperative triangle-tree kernels): the per-lane walk is a resumable state and the warp's walk loop yields once `walk_exit`
-    lanes hold a finished walk, so that they shade and regenerate instead of idling behind the longest walk.  Scheduling
-    only: bit-identical sums, ray counts and NaN redraws for every threshold (0 = walks run to completion, the old kernel)."""
-    W, H, pp = 200, 120, 5
-    sc = worlds(w).scene(W, H, lens=lens)
-    res = []
-    for t in (0, -1, 1, 6, 12, 20, 32):
-        rc = render.RenderCore(0)
-        rc.set_tuning(walk_exit=t)
-        rc.upload_scene(sc)
-        rc.render(W, H, pp, seed=13)
-        _, a, st = rc.readback(False, True)
-        res.append((a.copy(), st.rays, st.nan_retries))
-        rc.close()
-    for a, rays, nan in res[1:]:
-        assert np.array_equal(a.view(np.uint32), res[0][0].view(np.uint32))
-        assert rays == res[0][1] and nan == res[0][2]
-
-
 @pytest.mark.parametrize("batch", [1, 8, 32])
 def test_shade_deferral_does_not_change_the_samples(worlds, batch):
     """Parking lanes until `shade_batch` of them need a BRDF sample is scheduling only: bit-identical sums."""
@@ -441,9 +420,9 @@ def test_scene_reupload_is_stable(worlds):
 def test_tuning_is_validated_and_the_library_reads_no_environment(worlds, monkeypatch):
     L = render.lib()
     rc = render.RenderCore(0)
-    t = T.Tuning(C.sizeof(T.Tuning), -1, 0, -1, -1, 0, 0, -1, 0)
+    t = T.Tuning(C.sizeof(T.Tuning), -1, 0, -1, 0, 0, -1, 0)
     assert L.pt_set_tuning(rc._h, C.byref(t)) == 0
-    for field, bad in [("sample_lanes_log2", 6), ("shade_batch", 33), ("coop_max", 40), ("walk_exit", 33), ("tri_leaf", 65), ("wf_pixels_log2", 11)]:
+    for field, bad in [("sample_lanes_log2", 6), ("shade_batch", 33), ("coop_max", 40), ("tri_leaf", 65), ("wf_pixels_log2", 11)]:
         u = T.Tuning.from_buffer_copy(t)
         setattr(u, field, bad)
         assert L.pt_set_tuning(rc._h, C.byref(u)) == -1, field

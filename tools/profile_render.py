@@ -19,14 +19,13 @@ ap.add_argument("--lens", action="store_true")
 ap.add_argument("--lanes", type=int, default=-1)
 ap.add_argument("--shade-batch", type=int, default=0)
 ap.add_argument("--coop-max", type=int, default=-1)
-ap.add_argument("--walk-exit", type=int, default=-1)
 ap.add_argument("--tri-leaf", type=int, default=0)
 ap.add_argument("--sph-leaf", type=int, default=0)
 ap.add_argument("--json", action="store_true")
 a = ap.parse_args()
 k = {"auto": T.KERNEL_AUTO, "mega": T.KERNEL_MEGA, "wavefront": T.KERNEL_WAVEFRONT}[a.kernel]
 rc = render.RenderCore(0, bvh=T.BVH_DEVICE_LBVH if a.bvh == 'lbvh' else T.BVH_HOST_SAH, kernel=k)
-rc.set_tuning(sample_lanes_log2=a.lanes, shade_batch=a.shade_batch, coop_max=a.coop_max, walk_exit=a.walk_exit, tri_leaf=a.tri_leaf, sph_leaf=a.sph_leaf)
+rc.set_tuning(sample_lanes_log2=a.lanes, shade_batch=a.shade_batch, coop_max=a.coop_max, tri_leaf=a.tri_leaf, sph_leaf=a.sph_leaf)
 rc.upload_scene(host.HostWorld(a.world).scene(a.width, a.height, lens=a.lens))
 ms = []
 for i in range(a.frames):

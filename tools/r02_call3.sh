@@ -6,7 +6,7 @@ O=gpurun_out; mkdir -p $O
 ( timeout 1200 python -m pytest tests -m gpu -q > $O/r02c_pytest_gpu.txt 2>&1; echo "pytest exit $?" >> $O/r02c_pytest_gpu.txt )
 tail -6 $O/r02c_pytest_gpu.txt
 : > $O/r02c_resume_w5.jsonl
-for t in 0 4 8 12 16 20 24 28; do timeout 90 python tools/profile_render.py --world 5 --pp 16 --frames 3 --walk-exit $t --json | tail -1 >> $O/r02c_resume_w5.jsonl; done
+
 python -c "
 import json
 for l in open('$O/r02c_resume_w5.jsonl'):
