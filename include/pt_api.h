@@ -155,8 +155,10 @@ enum {
 
 /*
  * One pt_render call = samples [sample_begin, sample_end) of the p*p sample list of every pixel of
- * every 32x32 tile t (row-major tile order, main.cpp:888-904) with t % tile_count == tile_rank,
- * ADDED into the float4 accumulation buffer.  pp as g_pp (main.cpp:113): spp = pp*pp.
+ * every 32x32 tile (the reference's tile grid, main.cpp:888-904) that belongs to tile_rank,
+ * ADDED into the float4 accumulation buffer.  Tile (tx, ty) belongs to rank (tx + k * ty) % tile_count with k coprime
+ * to tile_count (pt_tile_owner): a diagonal interleave, so that no rank gets a vertical stripe of the image whatever the
+ * frame width.  Which rank renders a tile never changes its pixels (the RNG is keyed by pixel and sample).  pp as g_pp (main.cpp:113): spp = pp*pp.
  * sample index s = i*pp + j for the pinhole strata loop (main.cpp:1041-1042) and
  * s = rayIndex*pp + rayIndex2 for the lens loops (main.cpp:1114, 1145).
  * sample_end == 0 means pp*pp.  tile_count == 0 means 1.
@@ -225,7 +227,12 @@ int pt_readback(pt_context *ctx, uint32_t *bgra, float *accum_rgba, pt_stats *st
 /* device-side access for multi-GPU plumbing (NCCL reduce / gather run on these buffers) */
 int pt_device_buffers(pt_context *ctx, void **accum_rgba_dev, void **bgra_dev, int32_t *width, int32_t *height);
 int pt_set_stream(pt_context *ctx, void *cuda_stream);
-/* pack this rank's tiles (tile-major, 32*32 uint32 each, edge tiles zero-padded) / scatter a packed tile set back */
+/* Tile -> rank map: the owner of tile (tx, ty) of a width x height frame split over tile_count ranks, and (slot_out, may be
+ * NULL) the tile's slot in that rank's pack.  pt_tile_slots = slots per rank (the same for every rank; >= its tile count:
+ * a slot whose tile falls outside the grid is empty and packs as zeros). */
+uint32_t pt_tile_owner(int32_t width, int32_t height, uint32_t tile_count, uint32_t tx, uint32_t ty, uint32_t *slot_out);
+uint32_t pt_tile_slots(int32_t width, int32_t height, uint32_t tile_count);
+/* pack this rank's tile slots (slot-major, 32*32 uint32 each, zero-padded) / scatter a packed set back; *n_tiles_out = slots */
 int pt_pack_tiles(pt_context *ctx, void *dst_dev, uint32_t tile_rank, uint32_t tile_count, uint32_t *n_tiles_out);
 int pt_unpack_tiles(pt_context *ctx, const void *src_dev, uint32_t tile_rank, uint32_t tile_count);
 /* The same exchange in two kernels per frame instead of resolve + pack + (tile_count - 1) unpacks:
@@ -244,7 +251,7 @@ int pt_mark_resolved(pt_context *ctx);
  * ordered by events on the two contexts' streams -- the counterpart of the gather / reduce that
  * torch.distributed does for one process per GPU.  No reference counterpart (CPU threads share g_image,
  * main.cpp:107).
- *   pt_gather_tiles_from: resolve + pack src's tiles {t : t % tile_count == tile_rank}, copy them to dst's
+ *   pt_gather_tiles_from: resolve + pack the tiles of src that belong to tile_rank, copy them to dst's
  *                         device and unpack them into dst's BGRA frame.
  *   pt_add_accum_from:    dst.accum += src.accum (sample-range sharding); dst must be resolved again. */
 int pt_gather_tiles_from(pt_context *dst, pt_context *src, uint32_t tile_rank, uint32_t tile_count);
@@ -252,7 +259,7 @@ int pt_add_accum_from(pt_context *dst, pt_context *src);
 
 /* One process per GPU, direct tile exchange over NVLink peer memory (the fused "resolve + gather"): the root rank exports
  * its BGRA frame as a CUDA IPC handle, every other rank maps it, and pt_resolve_tiles_to resolves THIS rank's tiles
- * {t : t % tile_count == tile_rank} and stores the BGRA words straight into the mapped frame (one 128-byte row segment of a
+ * (pt_tile_owner == tile_rank) and stores the BGRA words straight into the mapped frame (one 128-byte row segment of a
  * tile per warp) -- no pack, no NCCL gather, no unpack.  The caller orders the ranks (a stream-ordered all-reduce of one
  * word before and after; pathtracer_b200/dist.py, mode "tiles_p2p").  No reference counterpart: the reference's worker
  * threads write their tiles into the one shared g_image (main.cpp:107, 862-866) -- this is that, across GPUs.

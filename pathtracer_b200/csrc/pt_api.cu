@@ -549,9 +549,7 @@ static int ensure_frame(pt_context *ctx, int w, int h) {
     return PT_OK;
 }
 
-static uint32_t my_tile_count(uint32_t n_tiles, uint32_t rank, uint32_t count) {
-    return rank < n_tiles ? (n_tiles - rank + count - 1) / count : 0;
-}
+static uint32_t slot_count(const PtTileMap &m) { return m.tiles_y * m.slots; }      // the same for every rank
 
 extern "C" int pt_render(pt_context *ctx, const pt_render_params *p) {
     if (!ctx || !p) return PT_ERR_INVALID_ARG;
@@ -578,10 +576,9 @@ extern "C" int pt_render(pt_context *ctx, const pt_render_params *p) {
     A.width = p->width; A.height = p->height; A.pp = p->pp;
     A.pp_magic = p->pp > 1 ? (uint32_t)(0x100000000ull / (uint64_t)p->pp + 1ull) : 0xFFFFFFFFu;   // pp == 1: s == 0 only
     A.s_begin = p->sample_begin; A.s_end = s_end;
-    A.tile_rank = p->tile_rank; A.tile_count = tile_count;
-    A.tiles_x = (uint32_t)(p->width + PT_TILE - 1) / PT_TILE;
-    A.tiles_y = (uint32_t)(p->height + PT_TILE - 1) / PT_TILE;
-    A.n_my_tiles = my_tile_count(A.tiles_x * A.tiles_y, p->tile_rank, tile_count);
+    A.tile_rank = p->tile_rank;
+    A.tiles = pt_tile_map(p->width, p->height, tile_count);
+    A.n_my_tiles = slot_count(A.tiles);
     A.seed = p->seed;
     A.accum = ctx->accum;
     A.counters = ctx->counters;
@@ -627,8 +624,10 @@ extern "C" int pt_render(pt_context *ctx, const pt_render_params *p) {
     // samples accounted on the host: pixels of my tiles x samples
     uint64_t px = 0;
     for (uint32_t j = 0; j < A.n_my_tiles; j++) {
-        uint32_t tile = p->tile_rank + j * tile_count;
-        uint32_t tx = (tile % A.tiles_x) * PT_TILE, ty = (tile / A.tiles_x) * PT_TILE;
+        uint32_t tx, ty;
+        pt_slot_tile(A.tiles, p->tile_rank, j, tx, ty);
+        if (tx >= A.tiles.tiles_x) continue;              // an empty slot
+        tx *= PT_TILE; ty *= PT_TILE;
         uint32_t w = std::min<uint32_t>(PT_TILE, (uint32_t)p->width - tx), h = std::min<uint32_t>(PT_TILE, (uint32_t)p->height - ty);
         px += (uint64_t)w * h;
     }
@@ -692,14 +691,24 @@ extern "C" int pt_device_buffers(pt_context *ctx, void **accum, void **bgra, int
     return PT_OK;
 }
 
+extern "C" uint32_t pt_tile_owner(int32_t width, int32_t height, uint32_t tile_count, uint32_t tx, uint32_t ty, uint32_t *slot_out) {
+    const PtTileMap tm = pt_tile_map(width, height, tile_count);
+    uint32_t r, j;
+    pt_tile_slot(tm, tx, ty, r, j);
+    if (slot_out) *slot_out = j;
+    return r;
+}
+
+extern "C" uint32_t pt_tile_slots(int32_t width, int32_t height, uint32_t tile_count) { return slot_count(pt_tile_map(width, height, tile_count)); }
+
 extern "C" int pt_pack_tiles(pt_context *ctx, void *dst, uint32_t rank, uint32_t count, uint32_t *n_out) {
     if (!ctx || !dst || count == 0 || rank >= count) return PT_ERR_INVALID_ARG;
     if (!ctx->bgra) return fail(ctx, PT_ERR_NO_FRAME, "pt_pack_tiles: nothing rendered yet");
     CK(cudaSetDevice(ctx->device));
-    uint32_t tiles_x = (uint32_t)(ctx->width + PT_TILE - 1) / PT_TILE, tiles_y = (uint32_t)(ctx->height + PT_TILE - 1) / PT_TILE;
-    uint32_t n = my_tile_count(tiles_x * tiles_y, rank, count);
+    const PtTileMap tm = pt_tile_map(ctx->width, ctx->height, count);
+    uint32_t n = slot_count(tm);
     if (n_out) *n_out = n;
-    if (n) k_pack_tiles<<<(n * 1024u + 255u) / 256u, 256, 0, ctx->stream>>>(ctx->bgra, (uint32_t *)dst, ctx->width, ctx->height, tiles_x, rank, count, n);
+    if (n) k_pack_tiles<<<(n * 1024u + 255u) / 256u, 256, 0, ctx->stream>>>(ctx->bgra, (uint32_t *)dst, ctx->width, ctx->height, tm, rank, n);
     CK(cudaGetLastError());
     return PT_OK;
 }
@@ -708,9 +717,9 @@ extern "C" int pt_unpack_tiles(pt_context *ctx, const void *src, uint32_t rank, 
     if (!ctx || !src || count == 0 || rank >= count) return PT_ERR_INVALID_ARG;
     if (!ctx->bgra) return fail(ctx, PT_ERR_NO_FRAME, "pt_unpack_tiles: nothing rendered yet");
     CK(cudaSetDevice(ctx->device));
-    uint32_t tiles_x = (uint32_t)(ctx->width + PT_TILE - 1) / PT_TILE, tiles_y = (uint32_t)(ctx->height + PT_TILE - 1) / PT_TILE;
-    uint32_t n = my_tile_count(tiles_x * tiles_y, rank, count);
-    if (n) k_unpack_tiles<<<(n * 1024u + 255u) / 256u, 256, 0, ctx->stream>>>(ctx->bgra, (const uint32_t *)src, ctx->width, ctx->height, tiles_x, rank, count, n);
+    const PtTileMap tm = pt_tile_map(ctx->width, ctx->height, count);
+    uint32_t n = slot_count(tm);
+    if (n) k_unpack_tiles<<<(n * 1024u + 255u) / 256u, 256, 0, ctx->stream>>>(ctx->bgra, (const uint32_t *)src, ctx->width, ctx->height, tm, rank, n);
     CK(cudaGetLastError());
     return PT_OK;
 }
@@ -719,10 +728,10 @@ extern "C" int pt_resolve_pack_tiles(pt_context *ctx, void *dst, uint32_t rank, 
     if (!ctx || !dst || count == 0 || rank >= count) return PT_ERR_INVALID_ARG;
     if (!ctx->accum) return fail(ctx, PT_ERR_NO_FRAME, "pt_resolve_pack_tiles: nothing rendered yet");
     CK(cudaSetDevice(ctx->device));
-    uint32_t tiles_x = (uint32_t)(ctx->width + PT_TILE - 1) / PT_TILE, tiles_y = (uint32_t)(ctx->height + PT_TILE - 1) / PT_TILE;
-    uint32_t n = my_tile_count(tiles_x * tiles_y, rank, count);
+    const PtTileMap tm = pt_tile_map(ctx->width, ctx->height, count);
+    uint32_t n = slot_count(tm);
     if (n_out) *n_out = n;
-    if (n) k_resolve_pack_tiles<<<(n * 1024u + 255u) / 256u, 256, 0, ctx->stream>>>(ctx->accum, (uint32_t *)dst, ctx->width, ctx->height, tiles_x, rank, count, n);
+    if (n) k_resolve_pack_tiles<<<(n * 1024u + 255u) / 256u, 256, 0, ctx->stream>>>(ctx->accum, (uint32_t *)dst, ctx->width, ctx->height, tm, rank, n);
     CK(cudaGetLastError());
     return PT_OK;
 }
@@ -731,10 +740,10 @@ extern "C" int pt_unpack_gathered(pt_context *ctx, const void *src, uint32_t cou
     if (!ctx || !src || count == 0) return PT_ERR_INVALID_ARG;
     if (!ctx->bgra) return fail(ctx, PT_ERR_NO_FRAME, "pt_unpack_gathered: no frame");
     CK(cudaSetDevice(ctx->device));
-    uint32_t tiles_x = (uint32_t)(ctx->width + PT_TILE - 1) / PT_TILE, tiles_y = (uint32_t)(ctx->height + PT_TILE - 1) / PT_TILE;
-    if (stride_words < my_tile_count(tiles_x * tiles_y, 0, count) * 1024u) return fail(ctx, PT_ERR_INVALID_ARG, "pt_unpack_gathered: stride shorter than rank 0's pack");
+    const PtTileMap tm = pt_tile_map(ctx->width, ctx->height, count);
+    if (stride_words < slot_count(tm) * 1024u) return fail(ctx, PT_ERR_INVALID_ARG, "pt_unpack_gathered: stride shorter than a rank's pack");
     uint32_t n = (uint32_t)ctx->width * (uint32_t)ctx->height;
-    k_unpack_gathered<<<(n + 255u) / 256u, 256, 0, ctx->stream>>>(ctx->bgra, (const uint32_t *)src, ctx->width, ctx->height, tiles_x, count, stride_words);
+    k_unpack_gathered<<<(n + 255u) / 256u, 256, 0, ctx->stream>>>(ctx->bgra, (const uint32_t *)src, ctx->width, ctx->height, tm, stride_words);
     CK(cudaGetLastError());
     ctx->resolved = true;          // the frame now holds every rank's resolved tiles
     return PT_OK;
@@ -830,15 +839,15 @@ extern "C" int pt_resolve_tiles_to(pt_context *ctx, void *dst_bgra, uint32_t ran
     if (!ctx || count == 0 || rank >= count) return PT_ERR_INVALID_ARG;
     if (!ctx->accum) return fail(ctx, PT_ERR_NO_FRAME, "pt_resolve_tiles_to: nothing rendered yet");
     CK(cudaSetDevice(ctx->device));
-    uint32_t tiles_x = (uint32_t)(ctx->width + PT_TILE - 1) / PT_TILE, tiles_y = (uint32_t)(ctx->height + PT_TILE - 1) / PT_TILE;
-    uint32_t n = my_tile_count(tiles_x * tiles_y, rank, count);
+    const PtTileMap tm = pt_tile_map(ctx->width, ctx->height, count);
+    uint32_t n = slot_count(tm);
     uint32_t *dst = dst_bgra ? (uint32_t *)dst_bgra : ctx->bgra;
     if (dst_bgra) {          // a destination other than the own frame must be a mapped peer frame of exactly this size
         bool ok = false;
         for (auto &m : ctx->peer_maps) ok = ok || (m.frame == dst_bgra && m.w == ctx->width && m.h == ctx->height);
         if (!ok) return fail(ctx, PT_ERR_INVALID_ARG, "pt_resolve_tiles_to: dst is not a peer frame mapped by this context with the same width x height");
     }
-    if (n) k_resolve_tiles_to<<<(n * 1024u + 255u) / 256u, 256, 0, ctx->stream>>>(ctx->accum, dst, ctx->width, ctx->height, tiles_x, rank, count, n);
+    if (n) k_resolve_tiles_to<<<(n * 1024u + 255u) / 256u, 256, 0, ctx->stream>>>(ctx->accum, dst, ctx->width, ctx->height, tm, rank, n);
     CK(cudaGetLastError());
     if (!dst_bgra) ctx->resolved = true;       // own frame: the caller vouches that peers fill the other ranks' tiles (pt_readback must not re-resolve)
     return PT_OK;
@@ -884,8 +893,8 @@ static int peer_prepare(pt_context *dst, pt_context *src, size_t bytes, const ch
 
 extern "C" int pt_gather_tiles_from(pt_context *dst, pt_context *src, uint32_t rank, uint32_t count) {
     if (!dst || !src || count == 0 || rank >= count) return PT_ERR_INVALID_ARG;
-    uint32_t tiles_x = (uint32_t)(src->width + PT_TILE - 1) / PT_TILE, tiles_y = (uint32_t)(src->height + PT_TILE - 1) / PT_TILE;
-    uint32_t n = my_tile_count(tiles_x * tiles_y, rank, count);
+    const PtTileMap tm = pt_tile_map(src->width, src->height, count);
+    uint32_t n = slot_count(tm);
     size_t bytes = (size_t)n * PT_TILE * PT_TILE * sizeof(uint32_t);
     int rc = peer_prepare(dst, src, bytes ? bytes : 16, "pt_gather_tiles_from");
     if (rc) return rc;
@@ -895,13 +904,13 @@ extern "C" int pt_gather_tiles_from(pt_context *dst, pt_context *src, uint32_t r
     if (!dst->resolved && (rc = pt_resolve(dst))) return rc;      // my own tiles first; the gathered ones overwrite theirs
     pt_context *ctx = dst;
     CK(cudaSetDevice(src->device));
-    k_pack_tiles<<<(n * 1024u + 255u) / 256u, 256, 0, src->stream>>>(src->bgra, (uint32_t *)src->pack_buf, src->width, src->height, tiles_x, rank, count, n);
+    k_pack_tiles<<<(n * 1024u + 255u) / 256u, 256, 0, src->stream>>>(src->bgra, (uint32_t *)src->pack_buf, src->width, src->height, tm, rank, n);
     if (dst->stage_in_use) CK(cudaStreamWaitEvent(src->stream, dst->ev_stage_free, 0));     // the previous unpack still reads the stage
     CK(cudaMemcpyPeerAsync(dst->stage_buf, dst->device, src->pack_buf, src->device, bytes, src->stream));
     CK(cudaEventRecord(src->ev_sent, src->stream));
     CK(cudaSetDevice(dst->device));
     CK(cudaStreamWaitEvent(dst->stream, src->ev_sent, 0));
-    k_unpack_tiles<<<(n * 1024u + 255u) / 256u, 256, 0, dst->stream>>>(dst->bgra, (const uint32_t *)dst->stage_buf, dst->width, dst->height, tiles_x, rank, count, n);
+    k_unpack_tiles<<<(n * 1024u + 255u) / 256u, 256, 0, dst->stream>>>(dst->bgra, (const uint32_t *)dst->stage_buf, dst->width, dst->height, tm, rank, n);
     CK(cudaEventRecord(dst->ev_stage_free, dst->stream));
     dst->stage_in_use = true;
     CK(cudaGetLastError());

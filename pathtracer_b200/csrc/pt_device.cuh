@@ -93,6 +93,47 @@ struct PtDeviceScene {
     uint32_t n_tri_clusters, n_sph_clusters;
 };
 
+// ---- tiles -> ranks ------------------------------------------------------------------------------
+// Tile (tx, ty) of the row-major 32x32 tile grid belongs to rank (tx + skew * ty) % count: a DIAGONAL interleave.  (The plain
+// "tile id % count" of round 1 degenerates to vertical stripes whenever the tile-row length is a multiple of count -- 1280 and
+// 3840 pixels at 8 ranks -- and the per-rank render times then spread by 6-10 %, profiles/r02e_scale_*.)  skew is coprime with
+// count, so every row and every run of `count` rows deals its tiles evenly.  A rank's tiles are enumerated by SLOT:
+// slot j = ty * slots + m with slots = ceil(tiles_x / count), tx = first(ty) + count * m; a slot whose tx falls outside the
+// grid is empty (the kernels' own x < width test skips it).  Every rank has tiles_y * slots slots: packs are equally long.
+struct PtTileMap {
+    uint32_t tiles_x, tiles_y, count, skew, slots;      // slots per tile row; n_slots = tiles_y * slots
+};
+__host__ __device__ inline uint32_t pt_tile_skew(uint32_t count) {
+    if (count <= 1) return 0;
+    uint32_t k = count / 2 + 1;
+    for (;; k++) {                                       // smallest k >= count/2 + 1 coprime with count
+        uint32_t a = k, b = count;
+        while (b) { uint32_t t = a % b; a = b; b = t; }
+        if (a == 1) return k % count;
+    }
+}
+__host__ __device__ inline PtTileMap pt_tile_map(int width, int height, uint32_t count) {
+    PtTileMap m;
+    m.tiles_x = (uint32_t)(width + PT_TILE - 1) / PT_TILE;
+    m.tiles_y = (uint32_t)(height + PT_TILE - 1) / PT_TILE;
+    m.count = count ? count : 1;
+    m.skew = pt_tile_skew(m.count);
+    m.slots = (m.tiles_x + m.count - 1) / m.count;
+    return m;
+}
+// slot j of `rank` -> tile coordinates; tx >= tiles_x (or ty >= tiles_y) marks an empty slot
+__host__ __device__ inline void pt_slot_tile(const PtTileMap &m, uint32_t rank, uint32_t j, uint32_t &tx, uint32_t &ty) {
+    ty = j / m.slots;
+    const uint32_t k = j - ty * m.slots;
+    const uint32_t first = (rank + m.count - (m.skew * ty) % m.count) % m.count;
+    tx = first + m.count * k;
+}
+// tile coordinates -> owning rank and its slot there
+__host__ __device__ inline void pt_tile_slot(const PtTileMap &m, uint32_t tx, uint32_t ty, uint32_t &rank, uint32_t &j) {
+    rank = (tx + m.skew * ty) % m.count;
+    j = ty * m.slots + tx / m.count;
+}
+
 struct PtHit {
     float t;
     uint32_t id;     // PT_ID(kind,index) or PT_ID_MISS

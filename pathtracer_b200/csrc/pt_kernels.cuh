@@ -38,8 +38,9 @@ struct PtRenderArgs {
     int width, height, pp;
     uint32_t pp_magic;                  // floor(2^32/pp)+1: s / pp == __umulhi(s, pp_magic) for s < pp*pp <= 10^6
     uint32_t s_begin, s_end;            // sample range of the pp*pp list
-    uint32_t tile_rank, tile_count;     // this launch renders tiles t with t % tile_count == tile_rank
-    uint32_t tiles_x, tiles_y, n_my_tiles;
+    uint32_t tile_rank;                 // this launch renders the tiles that tiles.{count, skew} deal to tile_rank (pt_device.cuh)
+    PtTileMap tiles;
+    uint32_t n_my_tiles;                // = tiles.tiles_y * tiles.slots: the rank's tile SLOTS (some may be empty)
     uint32_t log2_sample_lanes;         // S = lanes of a warp that share one pixel; P = 32/S pixels per warp
     uint32_t log2_pool_pixels;          // wavefront kernel: pixels per warp pool
     uint32_t shade_batch;               // megakernel, PT_F_DEFER variants: parked lanes before the BRDF code runs
@@ -131,8 +132,10 @@ k_render(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtRend
     const uint32_t tile_j = warp >> groups_per_tile_log2;
     const uint32_t grp = warp & ((1u << groups_per_tile_log2) - 1u);
     bool active = tile_j < A.n_my_tiles;
-    const uint32_t tile = A.tile_rank + tile_j * A.tile_count;
-    const uint32_t tx = (tile % A.tiles_x) * PT_TILE, ty = (tile / A.tiles_x) * PT_TILE;
+    uint32_t tx, ty;
+    pt_slot_tile(A.tiles, A.tile_rank, tile_j, tx, ty);      // an empty slot lands outside the image: inactive below
+    tx *= PT_TILE;
+    ty *= PT_TILE;
     const uint32_t gx = grp & ((1u << groups_x_log2) - 1u), gy = grp >> groups_x_log2;
     const uint32_t pig = lane >> lS, sl = lane & (Sn - 1u);
     const int x = (int)(tx + (gx << pw_log2) + (pig & ((1u << pw_log2) - 1u)));
@@ -415,35 +418,38 @@ __global__ void k_trace_paths(const __grid_constant__ PtDeviceScene S, const flo
 }
 
 // ---- tile pack / unpack for the multi-GPU gather --------------------------------------------------
-// packed layout: own tile j (tile id = rank + j*count) occupies 1024 uint32 at offset j*1024, row-major
-// inside the tile, pixels outside the image zero
+// packed layout: tile slot j of the rank (pt_slot_tile) occupies 1024 uint32 at offset j*1024, row-major inside the tile;
+// pixels outside the image -- and whole empty slots -- are zero
 __global__ void k_pack_tiles(const uint32_t *__restrict__ bgra, uint32_t *__restrict__ packed, int W, int H,
-                             uint32_t tiles_x, uint32_t rank, uint32_t count, uint32_t n_my_tiles) {
+                             const PtTileMap tm, uint32_t rank, uint32_t n_my_tiles) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_my_tiles * 1024u) return;
     uint32_t j = i >> 10, p = i & 1023u;
-    uint32_t tile = rank + j * count;
-    int x = (int)((tile % tiles_x) * PT_TILE + (p & 31u)), y = (int)((tile / tiles_x) * PT_TILE + (p >> 5));
+    uint32_t tx, ty;
+    pt_slot_tile(tm, rank, j, tx, ty);
+    int x = (int)(tx * PT_TILE + (p & 31u)), y = (int)(ty * PT_TILE + (p >> 5));
     packed[i] = (x < W && y < H) ? bgra[(size_t)y * W + x] : 0u;
 }
 __global__ void k_unpack_tiles(uint32_t *__restrict__ bgra, const uint32_t *__restrict__ packed, int W, int H,
-                               uint32_t tiles_x, uint32_t rank, uint32_t count, uint32_t n_my_tiles) {
+                               const PtTileMap tm, uint32_t rank, uint32_t n_my_tiles) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_my_tiles * 1024u) return;
     uint32_t j = i >> 10, p = i & 1023u;
-    uint32_t tile = rank + j * count;
-    int x = (int)((tile % tiles_x) * PT_TILE + (p & 31u)), y = (int)((tile / tiles_x) * PT_TILE + (p >> 5));
+    uint32_t tx, ty;
+    pt_slot_tile(tm, rank, j, tx, ty);
+    int x = (int)(tx * PT_TILE + (p & 31u)), y = (int)(ty * PT_TILE + (p >> 5));
     if (x < W && y < H) bgra[(size_t)y * W + x] = packed[i];
 }
 
 // resolve + pack in one pass: own tile j -> packed[j*1024 ..], resolved from the accumulator (no full-frame resolve first)
 __global__ void k_resolve_pack_tiles(const float4 *__restrict__ accum, uint32_t *__restrict__ packed, int W, int H,
-                                     uint32_t tiles_x, uint32_t rank, uint32_t count, uint32_t n_my_tiles) {
+                                     const PtTileMap tm, uint32_t rank, uint32_t n_my_tiles) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_my_tiles * 1024u) return;
     uint32_t j = i >> 10, p = i & 1023u;
-    uint32_t tile = rank + j * count;
-    int x = (int)((tile % tiles_x) * PT_TILE + (p & 31u)), y = (int)((tile / tiles_x) * PT_TILE + (p >> 5));
+    uint32_t tx, ty;
+    pt_slot_tile(tm, rank, j, tx, ty);
+    int x = (int)(tx * PT_TILE + (p & 31u)), y = (int)(ty * PT_TILE + (p >> 5));
     uint32_t v = 0u;
     if (x < W && y < H) {
         float4 a = accum[(size_t)y * W + x];
@@ -454,12 +460,12 @@ __global__ void k_resolve_pack_tiles(const float4 *__restrict__ accum, uint32_t 
 }
 // scatter the packs of ALL ranks (gathered back to back, `stride` words per rank) into the frame: one thread per pixel
 __global__ void k_unpack_gathered(uint32_t *__restrict__ bgra, const uint32_t *__restrict__ gathered, int W, int H,
-                                  uint32_t tiles_x, uint32_t count, uint32_t stride) {
+                                  const PtTileMap tm, uint32_t stride) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= (uint32_t)W * (uint32_t)H) return;
     uint32_t x = i % (uint32_t)W, y = i / (uint32_t)W;
-    uint32_t tile = (y / PT_TILE) * tiles_x + x / PT_TILE;
-    uint32_t r = tile % count, j = tile / count;
+    uint32_t r, j;
+    pt_tile_slot(tm, x / PT_TILE, y / PT_TILE, r, j);
     bgra[i] = gathered[(size_t)r * stride + j * 1024u + (y % PT_TILE) * PT_TILE + (x % PT_TILE)];
 }
 // resolve n pixels from any accumulator to any BGRA buffer (a rank's share after a reduce-scatter)
@@ -474,12 +480,13 @@ __global__ void k_resolve_range(const float4 *__restrict__ accum, uint32_t *__re
 // resolve this rank's tiles straight into a BGRA frame that may live on another GPU (mapped peer memory): thread i
 // handles pixel i & 1023 of own tile i >> 10, so a warp stores one 128-byte row segment of a tile
 __global__ void k_resolve_tiles_to(const float4 *__restrict__ accum, uint32_t *__restrict__ dst, int W, int H,
-                                   uint32_t tiles_x, uint32_t rank, uint32_t count, uint32_t n_my_tiles) {
+                                   const PtTileMap tm, uint32_t rank, uint32_t n_my_tiles) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_my_tiles * 1024u) return;
     uint32_t j = i >> 10, p = i & 1023u;
-    uint32_t tile = rank + j * count;
-    int x = (int)((tile % tiles_x) * PT_TILE + (p & 31u)), y = (int)((tile / tiles_x) * PT_TILE + (p >> 5));
+    uint32_t tx, ty;
+    pt_slot_tile(tm, rank, j, tx, ty);
+    int x = (int)(tx * PT_TILE + (p & 31u)), y = (int)(ty * PT_TILE + (p >> 5));
     if (x >= W || y >= H) return;
     float4 a = accum[(size_t)y * W + x];
     float inv = a.w > 0.f ? __fdiv_rn(1.0f, a.w) : 0.f;

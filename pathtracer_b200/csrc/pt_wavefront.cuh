@@ -67,9 +67,11 @@ k_render_wf(const __grid_constant__ PtDeviceScene S, const __grid_constant__ PtR
     const uint32_t tile_j = warp >> groups_per_tile_log2;
     const uint32_t grp = warp & ((1u << groups_per_tile_log2) - 1u);
     if (tile_j >= A.n_my_tiles) return;                                   // whole warp
-    const uint32_t tile = A.tile_rank + tile_j * A.tile_count;
+    uint32_t ttx, tty;
+    pt_slot_tile(A.tiles, A.tile_rank, tile_j, ttx, tty);
+    if (ttx >= A.tiles.tiles_x) return;                                   // an empty slot: whole warp
     const uint32_t gx = grp & ((1u << groups_x_log2) - 1u), gy = grp >> groups_x_log2;
-    const uint32_t x0 = (tile % A.tiles_x) * PT_TILE + (gx << pw_log2), y0 = (tile / A.tiles_x) * PT_TILE + (gy << ph_log2);
+    const uint32_t x0 = ttx * PT_TILE + (gx << pw_log2), y0 = tty * PT_TILE + (gy << ph_log2);
     // pool slot p: pixel-in-group q = p % P, sample slot sl = p / P
 #define WF_PIXEL_X(p) ((int)(x0 + (((p) & ((1u << lP) - 1u)) & ((1u << pw_log2) - 1u))))
 #define WF_PIXEL_Y(p) ((int)(y0 + (((p) & ((1u << lP) - 1u)) >> pw_log2)))

@@ -3,8 +3,8 @@
 The reference's only parallelism is CPU threads over 32x32 tiles handed out by MasterThread
 (src/win32_main.cpp:888-960).  Two partitions of the same work, both with exactly one exchange:
 
-  * "tiles"   rank r renders the tiles t with t % G == r (interleaved, so sky tiles and Mario tiles
-              spread evenly) and resolves them straight into a tile-major pack (pt_resolve_pack_tiles);
+  * "tiles"   rank r renders the tiles (tx, ty) with (tx + k*ty) % G == r (a diagonal interleave, k coprime
+              with G, so sky tiles and Mario tiles spread evenly whatever the frame width) and resolves them straight into a tile-major pack (pt_resolve_pack_tiles);
               the packs are GATHERED into one contiguous buffer on rank 0 (4 B/pixel in total, no
               reduction) and scattered into the frame by ONE kernel (pt_unpack_gathered).  Counter-based
               RNG keyed by (pixel, sample) => the frame is bit-identical for any G.
@@ -31,14 +31,50 @@ def tile_grid(width, height):
     return (width + TILE - 1) // TILE, (height + TILE - 1) // TILE
 
 
-def my_tiles(width, height, rank, world):
+def tile_skew(world):
+    """pt_tile_skew (csrc/pt_device.cuh): the smallest k >= world/2 + 1 coprime with world, mod world; 0 for one rank."""
+    from math import gcd
+    if world <= 1:
+        return 0
+    k = world // 2 + 1
+    while gcd(k, world) != 1:
+        k += 1
+    return k % world
+
+
+def slots_per_rank(width, height, world):
+    """Tile slots in every rank's pack (pt_tile_slots): tiles_y rows of ceil(tiles_x / world); some may be empty."""
     tx, ty = tile_grid(width, height)
-    return list(range(rank, tx * ty, world))
+    return ty * ((tx + world - 1) // world)
+
+
+def tile_owner(width, height, world, tx_, ty_):
+    """(rank, slot) of tile (tx_, ty_): rank = (tx + skew * ty) % world, slot = ty * slots_per_row + tx // world."""
+    tx, _ = tile_grid(width, height)
+    return (tx_ + tile_skew(world) * ty_) % world, ty_ * ((tx + world - 1) // world) + tx_ // world
+
+
+def tile_slots(width, height, rank, world):
+    """Row-major tile id held by each slot of `rank` (mirror of pt_slot_tile), -1 for an empty slot."""
+    tx, ty = tile_grid(width, height)
+    spr, k = (tx + world - 1) // world, tile_skew(world)
+    out = []
+    for y in range(ty):
+        first = (rank - k * y) % world
+        for m in range(spr):
+            x = first + world * m
+            out.append(y * tx + x if x < tx else -1)
+    return out
+
+
+def my_tiles(width, height, rank, world):
+    """Row-major ids of the tiles owned by `rank`, in slot order."""
+    return [t for t in tile_slots(width, height, rank, world) if t >= 0]
 
 
 def max_tiles_per_rank(width, height, world):
-    tx, ty = tile_grid(width, height)
-    return (tx * ty + world - 1) // world
+    """Length of a rank's pack in tiles (= slots_per_rank: equal for every rank)."""
+    return slots_per_rank(width, height, world)
 
 
 def sample_range(pp, rank, world):
@@ -50,12 +86,14 @@ def sample_range(pp, rank, world):
 
 
 def pack_tiles_host(bgra, rank, world):
-    """numpy mirror of k_pack_tiles (csrc/pt_kernels.cuh): [n_tiles, 32, 32] uint32, zero padded."""
+    """numpy mirror of k_pack_tiles (csrc/pt_kernels.cuh): [n_slots, 32, 32] uint32, zero padded (empty slots: zeros)."""
     h, w = bgra.shape
     tx, _ = tile_grid(w, h)
-    ids = my_tiles(w, h, rank, world)
+    ids = tile_slots(w, h, rank, world)
     out = np.zeros((len(ids), TILE, TILE), np.uint32)
     for j, t in enumerate(ids):
+        if t < 0:
+            continue
         x0, y0 = (t % tx) * TILE, (t // tx) * TILE
         blk = bgra[y0:y0 + TILE, x0:x0 + TILE]
         out[j, :blk.shape[0], :blk.shape[1]] = blk
@@ -66,7 +104,9 @@ def unpack_tiles_host(bgra, packed, rank, world):
     """numpy mirror of k_unpack_tiles."""
     h, w = bgra.shape
     tx, _ = tile_grid(w, h)
-    for j, t in enumerate(my_tiles(w, h, rank, world)):
+    for j, t in enumerate(tile_slots(w, h, rank, world)):
+        if t < 0:
+            continue
         x0, y0 = (t % tx) * TILE, (t // tx) * TILE
         hh, ww = min(TILE, h - y0), min(TILE, w - x0)
         bgra[y0:y0 + hh, x0:x0 + ww] = packed[j, :hh, :ww]
@@ -77,8 +117,10 @@ def unpack_gathered_host(gathered, width, height, world):
     """numpy mirror of k_unpack_gathered: `gathered` is [world, n_max*1024] uint32, rank r's pack in row r."""
     tx, _ = tile_grid(width, height)
     y, x = np.mgrid[0:height, 0:width]
-    tile = (y // TILE) * tx + x // TILE
-    return gathered[tile % world, (tile // world) * (TILE * TILE) + (y % TILE) * TILE + (x % TILE)]
+    spr = (tx + world - 1) // world
+    rank = (x // TILE + tile_skew(world) * (y // TILE)) % world
+    slot = (y // TILE) * spr + (x // TILE) // world
+    return gathered[rank, slot * (TILE * TILE) + (y % TILE) * TILE + (x % TILE)]
 
 
 def gather_packed_tiles(packed, width, height, group=None, out=None):

@@ -43,6 +43,10 @@ def lib():
         L.pt_unpack_gathered.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]
         L.pt_resolve_range.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32]
         L.pt_mark_resolved.argtypes = [C.c_void_p]
+        L.pt_tile_owner.argtypes = [C.c_int32, C.c_int32, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint32)]
+        L.pt_tile_owner.restype = C.c_uint32
+        L.pt_tile_slots.argtypes = [C.c_int32, C.c_int32, C.c_uint32]
+        L.pt_tile_slots.restype = C.c_uint32
         L.pt_render.argtypes = [C.c_void_p, C.POINTER(T.RenderParams)]
         L.pt_synchronize.argtypes = [C.c_void_p]
         L.pt_resolve.argtypes = [C.c_void_p]
@@ -73,7 +77,7 @@ EXPORTS = ["pt_api_version", "pt_create", "pt_destroy", "pt_last_error", "pt_upl
            "pt_pack_tiles", "pt_unpack_tiles", "pt_gather_tiles_from", "pt_add_accum_from", "pt_trace_rays", "pt_primary_hits", "pt_trace_paths",
            "pt_resolve_colors", "pt_measure_fp32_peak", "pt_flush_l2",
            "pt_frame_ipc_handle", "pt_open_peer_frame", "pt_close_peer_frame", "pt_resolve_tiles_to",
-           "pt_set_tuning", "pt_resolve_pack_tiles", "pt_unpack_gathered", "pt_resolve_range", "pt_mark_resolved"]
+           "pt_tile_owner", "pt_tile_slots", "pt_set_tuning", "pt_resolve_pack_tiles", "pt_unpack_gathered", "pt_resolve_range", "pt_mark_resolved"]
 
 
 def _p(a):
@@ -248,6 +252,7 @@ class RenderCore:
 
 
 def tile_ids(width, height, tile_rank, tile_count):
-    """Row-major ids of the 32x32 tiles (src/win32_main.cpp:888-904) owned by tile_rank."""
-    tx, ty = (width + 31) // 32, (height + 31) // 32
-    return list(range(tile_rank, tx * ty, tile_count))
+    """Row-major ids of the 32x32 tiles (src/win32_main.cpp:888-904) owned by tile_rank: tile (tx, ty) belongs to rank
+    (tx + k * ty) % tile_count (pt_tile_owner, include/pt_api.h)."""
+    from . import dist
+    return dist.my_tiles(width, height, tile_rank, tile_count)

@@ -45,7 +45,7 @@ def _worker(rank, world, port, mode, out_dir):
         if rank == 0:
             out = np.zeros((H, W), np.uint32)
             for r in range(world):
-                n = len(D.my_tiles(W, H, r, world))
+                n = D.slots_per_rank(W, H, world)
                 D.unpack_tiles_host(out, bufs[r].numpy().view(np.uint32)[:n * 1024].reshape(n, 32, 32), r, world)
             # the one-kernel scatter of the whole gathered buffer (k_unpack_gathered) must give the same frame
             assert np.array_equal(D.unpack_gathered_host(bufs.numpy().view(np.uint32), W, H, world), out)
@@ -103,7 +103,14 @@ def test_partitions_cover_exactly_once():
         for world in [1, 2, 3, 4, 8]:
             ids = sorted(t for r in range(world) for t in D.my_tiles(w, h, r, world))
             assert ids == list(range(tx * ty))
-            assert max(len(D.my_tiles(w, h, r, world)) for r in range(world)) == D.max_tiles_per_rank(w, h, world)
+            counts = [len(D.my_tiles(w, h, r, world)) for r in range(world)]
+            assert max(counts) <= D.slots_per_rank(w, h, world) and all(len(D.tile_slots(w, h, r, world)) == D.slots_per_rank(w, h, world) for r in range(world))
+            # the diagonal interleave deals every tile row evenly: shares differ by at most one tile per row
+            assert max(counts) - min(counts) <= ty
+            for r in range(world):
+                for j, t in enumerate(D.tile_slots(w, h, r, world)):
+                    if t >= 0:
+                        assert D.tile_owner(w, h, world, t % tx, t // tx) == (r, j)
     for pp in [0, 1, 3, 4, 23, 32]:
         for world in [1, 2, 3, 4, 8]:
             rs = [D.sample_range(pp, r, world) for r in range(world)]
@@ -111,6 +118,28 @@ def test_partitions_cover_exactly_once():
             assert all(a[1] == b[0] for a, b in zip(rs[:-1], rs[1:]))
             sizes = [b - a for a, b in rs]
             assert max(sizes) - min(sizes) <= 1
+
+
+def test_tile_map_matches_the_library():
+    """The Python mirror of the tile -> rank map (dist.tile_owner / tile_slots) equals the C one (pt_tile_owner,
+    pt_tile_slots): the kernels, the host accounting and the gloo tests agree on who owns which tile.  No vertical stripes:
+    at 1280 and 3840 pixels and 8 ranks (tile rows of 40 and 120) a rank's tiles are spread over every column class."""
+    import ctypes as C
+    from pathtracer_b200 import dist as D
+    from pathtracer_b200 import render
+    L = render.lib()
+    for (w, h) in [(1, 1), (33, 31), (300, 170), (1280, 720), (1920, 1080), (3840, 2160)]:
+        tx, ty = D.tile_grid(w, h)
+        for world in [1, 2, 3, 4, 5, 6, 7, 8]:
+            assert L.pt_tile_slots(w, h, world) == D.slots_per_rank(w, h, world)
+            for (x, y) in {(0, 0), (tx - 1, ty - 1), (tx // 2, ty // 3), (min(7, tx - 1), min(5, ty - 1))}:
+                slot = C.c_uint32()
+                r = L.pt_tile_owner(w, h, world, x, y, C.byref(slot))
+                assert (r, slot.value) == D.tile_owner(w, h, world, x, y)
+    for w, h in [(1280, 720), (3840, 2160)]:
+        tx, _ = D.tile_grid(w, h)
+        cols = {t % tx % 8 for t in D.my_tiles(w, h, 3, 8)}
+        assert cols == set(range(8))
 
 
 def test_pack_unpack_host_roundtrip():

@@ -56,7 +56,8 @@ def test_tile_pack_unpack_roundtrip(core, worlds):
     packs = []
     for r in range(G):
         _frame(core, W, H, pp, seed=5, tile_rank=r, tile_count=G)
-        n = len(render.tile_ids(W, H, r, G))
+        from pathtracer_b200 import dist as D
+        n = D.slots_per_rank(W, H, G)
         buf = torch.zeros(n * 1024, dtype=torch.int32, device="cuda")
         assert core.pack_tiles(buf.data_ptr(), r, G) == n
         core.synchronize()
@@ -340,7 +341,7 @@ def test_resolve_pack_and_one_kernel_unpack_equal_the_full_frame(core, worlds):
     for r in range(G):
         core.render(W, H, pp, seed=9, tile_rank=r, tile_count=G)
         n = core.resolve_pack_tiles(gathered[r].data_ptr(), r, G)
-        assert n == len(D.my_tiles(W, H, r, G))
+        assert n == D.slots_per_rank(W, H, G)
         core.synchronize()
     core.render(W, H, 0, seed=9)                       # empty accumulator: the frame must come from the packs alone
     core.unpack_gathered(gathered.data_ptr(), G, n_max)
