@@ -340,7 +340,8 @@ def test_brdf_branches_in_isolation_vs_oracle(core, name, material, just_cosine,
     camera -> sphere -> one sample of one BRDF branch -> sky or light, so a compensating pair of errors inside
     pt_shade_vertex (SchlickMetal, Hammon G / Burley alpha, GGX half vector, cosine hemisphere, cone sampling of the
     light, the mixture pdf, the orthonormal basis) cannot hide behind a whole-image average.  Tolerance 1e-5 relative
-    wherever no branch flips (a coin at 0.5 +- 1 ulp, a grazing N.L sign); such flips must stay below 0.2 % of rays."""
+    wherever no branch flips (a coin at 0.5 +- 1 ulp, a grazing N.L sign); such flips must stay below 0.2 % of rays
+    (0.8 % where the path has up to three shaded vertices), and must not move the mean."""
     sc = _one_sphere_scene(material, just_cosine, light)
     core.upload_scene(sc)
     rng = np.random.default_rng(5)
@@ -356,7 +357,10 @@ def test_brdf_branches_in_isolation_vs_oracle(core, name, material, just_cosine,
     scale = np.maximum(np.abs(want).max(1), 1e-3)
     rel = np.abs(got - want).max(1) / scale
     close = rel < 1e-5 * 20          # 1e-5 relative per operation chain; ~20 dependent float ops between draw and weight
-    assert close.mean() > 0.998, f"{name}: {100 * (1 - close.mean()):.3f} % of rays differ (max rel {rel.max():.3e})"
+    # with the black light the cone samples land on an ordinary surface and the path goes on for up to two more vertices:
+    # three times the chances of a flip per ray
+    flips_allowed = 0.002 if light else 0.008
+    assert close.mean() > 1 - flips_allowed, f"{name}: {100 * (1 - close.mean()):.3f} % of rays differ (max rel {rel.max():.3e})"
     assert np.median(rel) < 2e-6, np.median(rel)
     # the branch really ran: radiance is neither all-sky nor all-black, and the three channels separate where the material says so
     assert np.isfinite(got).all() and got.std() > 1e-3
