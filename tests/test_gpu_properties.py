@@ -523,3 +523,51 @@ def test_two_gpu_exchanges_give_the_one_gpu_frame(tmp_path, worlds):
         assert np.array_equal(got[f"tiles_p2p_{seed}"], b)
         assert (got[f"samples_{seed}"] == b).mean() > 0.999
     rc.close()
+
+
+def test_largest_baseline_frame_properties(core, worlds):
+    """C5's frame, 3840x2160 (the largest size BASELINE.json names): every pixel gets its samples, nothing is NaN or dropped,
+    two of eight tile ranks reproduce their pixels bit for bit (the diagonal tile map at a width whose tile row, 120, is a
+    multiple of 8), their shares are 1/8 of the frame, and no rank owns a vertical stripe."""
+    from pathtracer_b200 import dist as D
+    W, H, pp = 3840, 2160, 4
+    core.upload_scene(worlds(5).scene(W, H))
+    b, a, st = _frame(core, W, H, pp, seed=2)
+    assert st.samples == W * H * pp * pp and (a[..., 3] == pp * pp).all() and np.isfinite(a).all()
+    assert st.nan_dropped == 0 and (b >> 24 == 255).all()
+    for r in (1, 6):
+        _, ar, sr = _frame(core, W, H, pp, seed=2, tile_rank=r, tile_count=8)
+        mine = ar[..., 3] > 0
+        assert np.array_equal(ar[mine], a[mine]) and sr.samples == mine.sum() * pp * pp
+        assert abs(mine.mean() - 1 / 8) < 0.005
+        cols = np.unique(np.nonzero(mine.any(0))[0] // 32)
+        assert len(cols) == 120                                   # tiles in every tile column: not a stripe
+        tx, _ = D.tile_grid(W, H)
+        ids = D.my_tiles(W, H, r, 8)
+        t = ids[len(ids) // 2]
+        assert mine[(t // tx) * 32:(t // tx) * 32 + 32, (t % tx) * 32:(t % tx) * 32 + 32].all()
+
+
+@pytest.mark.parametrize("w", [1, 2, 3, 4, 5])
+def test_no_sample_is_dropped_or_nan_on_any_world(core, worlds, w):
+    """The reference redraws a NaN sample for ever (main.cpp:1068); the kernel redraws up to 8 times and then reports the
+    sample in pt_stats.nan_dropped.  On the five worlds that counter stays 0 and every accumulator is finite."""
+    W, H, pp = 320, 180, 8
+    core.upload_scene(worlds(w).scene(W, H))
+    _, a, st = _frame(core, W, H, pp, seed=17)
+    assert st.nan_dropped == 0 and np.isfinite(a).all() and (a[..., 3] == pp * pp).all()
+    assert st.nan_retries < 1e-4 * st.samples
+
+
+def test_set_camera_keeps_the_scene(core, worlds):
+    """pt_set_camera swaps the camera without touching the arena or the BVH: switching pinhole -> thin lens -> pinhole on an
+    uploaded scene gives the images fresh uploads of those scenes give (the kernel variant follows the camera)."""
+    W, H, pp = 120, 80, 4
+    out = {}
+    for lens in (False, True):
+        core.upload_scene(worlds(5).scene(W, H, lens=lens))
+        out[lens] = _frame(core, W, H, pp, seed=9)[1]
+    core.upload_scene(worlds(5).scene(W, H, lens=False))
+    for lens in (True, False, True):
+        core.set_camera(worlds(5).scene(W, H, lens=lens).camera)
+        assert np.array_equal(_frame(core, W, H, pp, seed=9)[1], out[lens])
