@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Kernel time of every rank's share of one frame (tile sharding), measured on ONE GPU: load balance of the
-tile -> rank assignment.  usage: tools/tile_balance.py [G] [world] [W] [H] [pp]"""
+tile -> rank assignment.  usage: tools/tile_balance.py [G] [world] [W] [H] [pp] [sample_lanes_log2 | -1]"""
 import os, sys
 ROOT = os.path.abspath(os.path.join(os.path.dirname(__file__), ".."))
 sys.path.insert(0, ROOT)
@@ -10,7 +10,9 @@ w = int(sys.argv[2]) if len(sys.argv) > 2 else 5
 W = int(sys.argv[3]) if len(sys.argv) > 3 else 1920
 H = int(sys.argv[4]) if len(sys.argv) > 4 else 1080
 pp = int(sys.argv[5]) if len(sys.argv) > 5 else 32
+lanes = int(sys.argv[6]) if len(sys.argv) > 6 else -1
 rc = render.RenderCore(0)
+rc.set_tuning(sample_lanes_log2=lanes)
 rc.upload_scene(host.HostWorld(w).scene(W, H))
 rc.render(W, H, pp, seed=1)
 _, _, st = rc.readback(False, False)
