@@ -598,8 +598,12 @@ extern "C" int pt_render(pt_context *ctx, const pt_render_params *p) {
             // full frame, but a warp then carries 4x the work and the last warps of a launch run alone: the tail costs
             // ~ 1/(lanes x pixels).  A small share of a frame (multi-GPU tiles) therefore takes more lanes per pixel:
             // lanes x pixels >= 7 M  (profiles/r01e_tile_balance.txt: 1/8 of 1080p, 74 % -> 96 % of the ideal share).
+            // Sphere trees are the exception: their walks are long and incoherent whatever the launch shape, and 8 lanes x 4 pixels
+            // wins at every share size measured (w4 1/8 of 1080p: 5.88 ms vs 6.57 ms at 32 lanes, w2 1/8 of 720p: 3.27 vs 3.41;
+            // profiles/r02j_lanes_for_shares.txt, r02k_lanes_for_shares_spheres.txt).
+            const bool sphere_tree_only = ctx->scene.sphere_bvh.n_nodes != 0 && ctx->scene.tri_bvh.n_nodes == 0;
             uint32_t lS_auto = 3u;
-            while (lS_auto < 5u && ((uint64_t)A.n_my_tiles * 1024u << lS_auto) < (7ull << 20)) lS_auto++;
+            while (!sphere_tree_only && lS_auto < 5u && ((uint64_t)A.n_my_tiles * 1024u << lS_auto) < (7ull << 20)) lS_auto++;
             lS = std::min<uint32_t>(lS, ctx->sample_lanes_log2 >= 0 ? (uint32_t)ctx->sample_lanes_log2 : lS_auto);
             A.log2_sample_lanes = lS;
             // parked lanes before the BRDF code runs (variants with PT_F_DEFER): measured best 32 with textures, else 20
