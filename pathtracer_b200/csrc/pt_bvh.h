@@ -6,6 +6,8 @@
 #include <cfloat>
 #include <cmath>
 #include <cstdint>
+#include <cstring>
+#include <xmmintrin.h>
 #include <vector>
 
 namespace ptbvh {
@@ -46,6 +48,11 @@ public:
         cent_.resize(boxes_.size() * 3);
         for (size_t i = 0; i < boxes_.size(); i++)
             for (int k = 0; k < 3; k++) cent_[3 * i + k] = 0.5f * (boxes_[i].mn[k] + boxes_[i].mx[k]);
+        box4_.resize(boxes_.size());
+        for (size_t i = 0; i < boxes_.size(); i++) {
+            box4_[i].mn = _mm_set_ps(0.f, boxes_[i].mn[2], boxes_[i].mn[1], boxes_[i].mn[0]);
+            box4_[i].mx = _mm_set_ps(0.f, boxes_[i].mx[2], boxes_[i].mx[1], boxes_[i].mx[0]);
+        }
     }
 
     Result build() {
@@ -71,7 +78,7 @@ public:
             return r;
         }
         r.nodes.emplace_back();
-        split(0, 0, n, 1);
+        split(0, 0, n, 1, -1);
         return r;
     }
 
@@ -90,32 +97,93 @@ private:
         return b;
     }
 
-    // exact sweep SAH for small ranges: sort by centroid on each axis and evaluate every split position
-    uint32_t partition_sweep(uint32_t first, uint32_t last) {
-        const uint32_t n = last - first;
-        float best_cost = FLT_MAX; int best_axis = -1; uint32_t best_k = 0;
-        std::vector<uint32_t> idx(n), best_order;
-        std::vector<float> right_area(n);
-        for (int ax = 0; ax < 3; ax++) {
-            for (uint32_t i = 0; i < n; i++) idx[i] = out_->order[first + i];
-            std::stable_sort(idx.begin(), idx.end(), [&](uint32_t a, uint32_t b) { return cent_[3 * a + ax] < cent_[3 * b + ax]; });
-            Box acc; acc.reset();
-            for (uint32_t i = n; i-- > 1;) { acc.grow(boxes_[idx[i]]); right_area[i] = acc.area(); }
-            acc.reset();
-            for (uint32_t k = 1; k < n; k++) {                 // left = idx[0..k), right = idx[k..n)
-                acc.grow(boxes_[idx[k - 1]]);
-                float cost = acc.area() * (float)k + right_area[k] * (float)(n - k);
-                if (cost < best_cost) { best_cost = cost; best_axis = ax; best_k = k; best_order = idx; }
+    // exact sweep SAH for small ranges: sort by centroid on each axis and evaluate every split position.
+    // Host time matters here: the BVH build is most of pt_upload_scene, i.e. of the end-to-end overhead per frame at 8 GPUs.
+    // Same splits and the same tree as the plain formulation (a std::stable_sort of the range per axis, scalar boxes), but
+    //   * the stable sort is a stable LSD radix sort of the ordered float bits (4 passes of 8 bits; a comparison sort of 752 keys
+    //     is ~7 000 badly predicted branches, and it ran three times per node), insertion sort below 48 elements;
+    //   * the axis the PARENT split on needs no sort: the incoming order is that sort, ties included;
+    //   * boxes are swept as two SSE registers (min, max) -- a grow is two instructions.
+    struct Box4 {
+        __m128 mn, mx;
+        void reset() { mn = _mm_set1_ps(FLT_MAX); mx = _mm_set1_ps(-FLT_MAX); }
+        void grow(const Box4 &b) { mn = _mm_min_ps(mn, b.mn); mx = _mm_max_ps(mx, b.mx); }
+        float area() const {                               // == Box::area(): 2 (dx dy + dy dz + dz dx), 0 for an empty box
+            const __m128 d = _mm_sub_ps(mx, mn);
+            alignas(16) float e[4];
+            _mm_store_ps(e, d);
+            if (e[0] < 0 || e[1] < 0 || e[2] < 0) return 0.f;
+            return 2.f * (e[0] * e[1] + e[1] * e[2] + e[2] * e[0]);
+        }
+    };
+
+    // idx <- order[first, first + n) stably sorted by the centroid along ax (ties keep the incoming order, as std::stable_sort would)
+    void sort_by_centroid(uint32_t first, uint32_t n, int ax, std::vector<uint32_t> &idx) {
+        keys_.resize(2 * (size_t)n);
+        uint64_t *a = keys_.data(), *b = a + n;               // (ordered float bits << 32) | primitive
+        for (uint32_t i = 0; i < n; i++) {
+            const uint32_t p = out_->order[first + i];
+            uint32_t bits;
+            const float c = cent_[3 * p + ax];
+            std::memcpy(&bits, &c, 4);
+            if (bits == 0x80000000u) bits = 0;                                   // -0 == +0, as operator< has it
+            bits = (bits & 0x80000000u) ? ~bits : (bits | 0x80000000u);          // the floats' order; centroids are never NaN
+            a[i] = ((uint64_t)bits << 32) | p;
+        }
+        if (n < 48) {
+            for (uint32_t i = 1; i < n; i++) {                                   // stable insertion sort on the float bits only
+                const uint64_t v = a[i];
+                uint32_t j = i;
+                while (j > 0 && (a[j - 1] >> 32) > (v >> 32)) { a[j] = a[j - 1]; j--; }
+                a[j] = v;
+            }
+        } else {
+            for (int pass = 0; pass < 4; pass++) {
+                const int shift = 32 + 8 * pass;
+                uint32_t count[257] = {0};
+                for (uint32_t i = 0; i < n; i++) count[((a[i] >> shift) & 255u) + 1]++;
+                if (count[((a[0] >> shift) & 255u) + 1] == n) continue;          // every key has this digit: the pass is the identity
+                for (int d = 0; d < 256; d++) count[d + 1] += count[d];
+                for (uint32_t i = 0; i < n; i++) b[count[(a[i] >> shift) & 255u]++] = a[i];
+                std::swap(a, b);
             }
         }
+        for (uint32_t i = 0; i < n; i++) idx[i] = (uint32_t)a[i];
+    }
+
+    uint32_t partition_sweep(uint32_t first, uint32_t last, int sorted_axis, int *axis_out) {
+        const uint32_t n = last - first;
+        float best_cost = FLT_MAX; int best_axis = -1; uint32_t best_k = 0;
+        if (right_area_.size() < n) right_area_.resize(n);
+        for (int ax = 0; ax < 3; ax++) {
+            std::vector<uint32_t> &idx = idx_[ax];
+            idx.resize(n);
+            if (ax == sorted_axis) {
+                for (uint32_t i = 0; i < n; i++) idx[i] = out_->order[first + i];
+            } else {
+                sort_by_centroid(first, n, ax, idx);
+            }
+            Box4 acc; acc.reset();
+            for (uint32_t i = n; i-- > 1;) { acc.grow(box4_[idx[i]]); right_area_[i] = acc.area(); }
+            acc.reset();
+            for (uint32_t k = 1; k < n; k++) {                 // left = idx[0..k), right = idx[k..n)
+                acc.grow(box4_[idx[k - 1]]);
+                float cost = acc.area() * (float)k + right_area_[k] * (float)(n - k);
+                if (cost < best_cost) { best_cost = cost; best_axis = ax; best_k = k; }
+            }
+        }
+        *axis_out = best_axis;
         if (best_axis < 0) return first + n / 2;
-        for (uint32_t i = 0; i < n; i++) out_->order[first + i] = best_order[i];
+        std::copy(idx_[best_axis].begin(), idx_[best_axis].end(), out_->order.begin() + first);
         return first + best_k;
     }
 
     // chooses the split of [first,last) and returns mid; falls back to a median split when SAH finds nothing
-    uint32_t partition(uint32_t first, uint32_t last) {
-        if (sweep_ && last - first <= 4096) return partition_sweep(first, last);
+    // sorted_axis: the axis along which [first,last) is already sorted (the parent's sweep split), -1 = none; *axis_out = the
+    // axis this split leaves the two halves sorted along (-1 after a binned or median split)
+    uint32_t partition(uint32_t first, uint32_t last, int sorted_axis, int *axis_out) {
+        if (sweep_ && last - first <= 4096) return partition_sweep(first, last, sorted_axis, axis_out);
+        *axis_out = -1;
         const int NB = 16;
         Box cb; cb.reset();
         for (uint32_t i = first; i < last; i++) cb.grow(&cent_[3 * out_->order[i]]);
@@ -161,7 +229,7 @@ private:
         return mid;
     }
 
-    int32_t make_child(uint32_t first, uint32_t last, int depth, Box &box_out) {
+    int32_t make_child(uint32_t first, uint32_t last, int depth, Box &box_out, int sorted_axis) {
         box_out = range_box(first, last);
         pad(box_out);
         uint32_t n = last - first;
@@ -171,15 +239,16 @@ private:
         }
         uint32_t idx = (uint32_t)out_->nodes.size();
         out_->nodes.emplace_back();
-        split(idx, first, last, depth + 1);
+        split(idx, first, last, depth + 1, sorted_axis);
         return (int32_t)idx;
     }
 
-    void split(uint32_t node, uint32_t first, uint32_t last, int depth) {
-        uint32_t mid = partition(first, last);
+    void split(uint32_t node, uint32_t first, uint32_t last, int depth, int sorted_axis) {
+        int axis = -1;
+        uint32_t mid = partition(first, last, sorted_axis, &axis);
         Box lb, rb;
-        int32_t l = make_child(first, mid, depth, lb);
-        int32_t r = make_child(mid, last, depth, rb);
+        int32_t l = make_child(first, mid, depth, lb, axis);
+        int32_t r = make_child(mid, last, depth, rb, axis);
         Node &n = out_->nodes[node];
         store_child_box(n, 0, lb);
         store_child_box(n, 1, rb);
@@ -188,6 +257,10 @@ private:
 
     const std::vector<Box> &boxes_;
     std::vector<float> cent_;
+    std::vector<Box4> box4_;          // the same boxes as (min, max) SSE pairs for the sweeps
+    std::vector<uint32_t> idx_[3];    // partition_sweep scratch: the range sorted along each axis
+    std::vector<float> right_area_;
+    std::vector<uint64_t> keys_;
     int max_leaf_;
     bool sweep_ = true;       // exact SAH below 4096 primitives per range, 16 bins above
     Result *out_ = nullptr;

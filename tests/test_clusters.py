@@ -86,3 +86,45 @@ def test_sphere_worlds_have_a_cut(checker, worlds, world):
     boxes = np.concatenate([c - r, c + r], 1)[small]
     rc, st = checker(boxes, None, 2)
     assert rc == 0 and st.partition_ok and st.contain_ok and 2 <= st.n_clusters <= 32
+
+
+def test_fast_sah_builder_builds_the_identical_tree(tmp_path_factory):
+    """pt_bvh.h sorts with a stable radix sort, skips the axis the parent already sorted and sweeps SSE boxes (the BVH build is
+    most of the host time of pt_upload_scene).  Against the plain formulation of the same algorithm (tests/cpp/bvh_check.cpp:
+    std::stable_sort per axis per node, scalar boxes) the tree must be IDENTICAL -- nodes bit for bit, primitive order, depth --
+    on random boxes, on the worlds' own primitives, and on inputs full of ties (grids, coincident centroids, -0.0)."""
+    so = str(tmp_path_factory.mktemp("bvh") / "libbvh_check.so")
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-shared", "-fPIC", "-I" + os.path.join(ROOT, "pathtracer_b200", "csrc"),
+                           "-I" + os.path.join(ROOT, "include"), "-o", so, os.path.join(ROOT, "tests", "cpp", "bvh_check.cpp")])
+    L = C.CDLL(so)
+    L.bvh_check.argtypes = [C.c_void_p, C.c_uint32, C.c_int]
+
+    def check(boxes, leaf):
+        boxes = np.ascontiguousarray(boxes, np.float32)
+        assert L.bvh_check(boxes.ctypes.data_as(C.c_void_p), len(boxes), leaf) == 0, (len(boxes), leaf)
+
+    rng = np.random.default_rng(3)
+    for n in (5, 47, 48, 49, 200, 752, 3000):
+        c = rng.uniform(-3, 3, (n, 3))
+        h = rng.uniform(0.01, 0.3, (n, 3))
+        for leaf in (1, 3, 4):
+            check(np.hstack([c - h, c + h]), leaf)
+    # ties everywhere: a grid of equal spheres in a plane (world 2 / 4 style), coincident boxes, zero and negative-zero centroids
+    g = np.stack(np.meshgrid(np.arange(11) * 0.5, np.arange(11) * 0.5, [0.2]), -1).reshape(-1, 3)
+    check(np.hstack([g - 0.2, g + 0.2]), 3)
+    same = np.tile([[-1, -1, -1, 1, 1, 1]], (70, 1)).astype(np.float32)
+    check(same, 2)
+    z = np.zeros((100, 6), np.float32)
+    z[:, 0] = -rng.integers(0, 3, 100); z[:, 3] = -z[:, 0]                   # centroids exactly +0 ... and
+    z[::2, 1], z[::2, 4] = -0.0, -0.0                                        # ... -0.0 on another axis
+    z[:, 2] = rng.integers(0, 4, 100); z[:, 5] = z[:, 2] + 1
+    check(z, 2)
+    # the worlds' own trees: Mario's triangles, the sphere fields of worlds 2 and 4
+    s5 = host.scene_arrays(host.HostWorld(5).scene(64, 36))
+    t = s5["tri_points"].reshape(-1, 3, 3)
+    check(np.hstack([t.min(1), t.max(1)]), 4)
+    for w in (2, 4):
+        sp = host.scene_arrays(host.HostWorld(w).scene(64, 36))["spheres"]
+        c, r = sp["p"], sp["r"][:, None]
+        keep = sp["r"] < 16 * np.median(sp["r"])
+        check(np.hstack([c - r, c + r])[keep], 3)
