@@ -284,6 +284,17 @@ int pt_primary_hits(pt_context *ctx, int32_t width, int32_t height, pt_hit *hits
 int pt_trace_paths(pt_context *ctx, uint32_t n, const float *origins, const float *dirs, uint64_t seed, float *rgb_out);
 /* resolve n HDR colours (n*3 floats, host) to BGRA8 exactly as pt_resolve does */
 int pt_resolve_colors(pt_context *ctx, uint32_t n, const float *rgb, uint32_t *bgra_out);
+/* The same as pt_resolve_colors for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  NO COUNTERPART IN THE REFERENCE.  It allocates nothing -- no
+ * cudaMalloc / cudaFree, no allocating library routine: the staging that pt_resolve_colors allocates per call lives in a fixed
+ * 1 MiB device array inside the library (held by every GPU that loads the library until the process exits), so
+ * n <= PT_NOALLOC_MAX_COLORS; a larger n is rejected with PT_ERR_UNSUPPORTED and a message (split the call, or use
+ * pt_resolve_colors).  rgb and bgra_out are HOST pointers supplied by the caller, as for pt_resolve_colors; results are
+ * byte-identical to it.  The scratch area is shared by every call on the same GPU and keeps the last call's contents (nothing
+ * in it needs to start at zero: each call overwrites what it reads); calls that overlap on the GPU -- contexts on different
+ * streams with no ordering between them -- race on it.  The call returns after its own work has finished. */
+#define PT_NOALLOC_MAX_COLORS 65536u
+int pt_resolve_colors_noalloc(pt_context *ctx, uint32_t n, const float *rgb, uint32_t *bgra_out);
 
 /* measurement helper for the roofline: achieved FP32 FMA throughput of this device (TFLOP/s, best of 5
    runs of an 8-way-ILP FMA chain on every SM), timed with CUDA events on the context's stream */

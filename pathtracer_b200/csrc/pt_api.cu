@@ -1026,6 +1026,50 @@ extern "C" int pt_resolve_colors(pt_context *ctx, uint32_t n, const float *rgb, 
     return PT_OK;
 }
 
+// ---- pt_resolve_colors without any allocation ------------------------------------------------------------------
+// pt_resolve_colors stages its input colours and its output words in two device buffers it cudaMallocs and frees per call.
+// Callers that must not allocate (CUDA graph capture, tight serving loops, harnesses that forbid it) get the same kernel over
+// a FIXED scratch area: a file-scope device array, 1 MiB, held by every GPU that loads the library until the process exits.
+// Layout: [0, 12 * MAX) the n x 3 input floats, [12 * MAX, 16 * MAX) the n output words.
+// In host code the array's NAME is a host-side stand-in, not a device address: the address comes from cudaGetSymbolAddress,
+// once per device, with that device current (noalloc_scratch below).  Nothing in the scratch has to start at zero: every
+// call overwrites the ranges it reads.  All calls -- of every context on the same device -- share the array: calls that
+// overlap on the GPU (different streams, no ordering between them) race.
+static __device__ __align__(256) unsigned char g_pt_noalloc_scratch[(size_t)PT_NOALLOC_MAX_COLORS * 16];
+
+static int noalloc_scratch(pt_context *ctx, unsigned char **out) {
+    static unsigned char *per_device[64] = {nullptr};      // filled once per device; a benign race writes the same value twice
+    if (ctx->device < 0 || ctx->device >= 64) return fail(ctx, PT_ERR_UNSUPPORTED, "pt_resolve_colors_noalloc: device ordinal beyond 63");
+    if (!per_device[ctx->device]) {
+        void *p = nullptr;
+        CK(cudaGetSymbolAddress(&p, g_pt_noalloc_scratch));       // ctx->device is current (set by the caller below)
+        if (!p) return fail(ctx, PT_ERR_CUDA, "pt_resolve_colors_noalloc: cudaGetSymbolAddress returned NULL");
+        per_device[ctx->device] = (unsigned char *)p;
+    }
+    *out = per_device[ctx->device];
+    return PT_OK;
+}
+
+extern "C" int pt_resolve_colors_noalloc(pt_context *ctx, uint32_t n, const float *rgb, uint32_t *out) {
+    if (!ctx || !rgb || !out) return PT_ERR_INVALID_ARG;
+    if (n > PT_NOALLOC_MAX_COLORS)
+        return fail(ctx, PT_ERR_UNSUPPORTED, "pt_resolve_colors_noalloc: n = " + std::to_string(n) + " exceeds PT_NOALLOC_MAX_COLORS = " +
+                                                 std::to_string(PT_NOALLOC_MAX_COLORS) + " (the fixed scratch area); split the call or use pt_resolve_colors");
+    if (n == 0) return PT_OK;
+    CK(cudaSetDevice(ctx->device));
+    unsigned char *scratch = nullptr;
+    int rc = noalloc_scratch(ctx, &scratch);
+    if (rc) return rc;
+    float *dC = reinterpret_cast<float *>(scratch);
+    uint32_t *dB = reinterpret_cast<uint32_t *>(scratch + (size_t)PT_NOALLOC_MAX_COLORS * 12);
+    CK(cudaMemcpyAsync(dC, rgb, (size_t)n * 12, cudaMemcpyHostToDevice, ctx->stream));
+    k_resolve_colors<<<(n + 255) / 256, 256, 0, ctx->stream>>>(dC, dB, n);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(out, dB, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return PT_OK;
+}
+
 extern "C" int pt_measure_fp32_peak(pt_context *ctx, float *tflops_out) {
     if (!ctx || !tflops_out) return PT_ERR_INVALID_ARG;
     CK(cudaSetDevice(ctx->device));

@@ -15,6 +15,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # PT_B200_LIB: another build of the same library (kernel experiments: tools/build_variants.sh)
 LIB_PATH = os.environ.get("PT_B200_LIB") or os.path.join(_HERE, "libpt_b200.so")
 
+NOALLOC_MAX_COLORS = 65536  # PT_NOALLOC_MAX_COLORS
 IPC_HANDLE_BYTES = 80       # PT_IPC_HANDLE_BYTES
 _lib = None
 
@@ -67,6 +68,7 @@ def lib():
         L.pt_primary_hits.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]
         L.pt_trace_paths.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
         L.pt_resolve_colors.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]
+        L.pt_resolve_colors_noalloc.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]
         L.pt_measure_fp32_peak.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
         _lib = L
     return _lib
@@ -75,7 +77,7 @@ def lib():
 EXPORTS = ["pt_api_version", "pt_create", "pt_destroy", "pt_last_error", "pt_upload_scene", "pt_set_camera",
            "pt_render", "pt_synchronize", "pt_resolve", "pt_readback", "pt_device_buffers", "pt_set_stream",
            "pt_pack_tiles", "pt_unpack_tiles", "pt_gather_tiles_from", "pt_add_accum_from", "pt_trace_rays", "pt_primary_hits", "pt_trace_paths",
-           "pt_resolve_colors", "pt_measure_fp32_peak", "pt_flush_l2",
+           "pt_resolve_colors", "pt_resolve_colors_noalloc", "pt_measure_fp32_peak", "pt_flush_l2",
            "pt_frame_ipc_handle", "pt_open_peer_frame", "pt_close_peer_frame", "pt_resolve_tiles_to",
            "pt_tile_owner", "pt_tile_slots", "pt_set_tuning", "pt_resolve_pack_tiles", "pt_unpack_gathered", "pt_resolve_range", "pt_mark_resolved"]
 
@@ -244,6 +246,13 @@ class RenderCore:
         self._ck(lib().pt_resolve_colors(self._h, rgb.shape[0], _p(rgb), _p(out)))
         return out
 
+
+    def resolve_colors_noalloc(self, rgb):
+        """pt_resolve_colors_noalloc: the same result with no device allocation (n <= NOALLOC_MAX_COLORS)."""
+        rgb = np.ascontiguousarray(rgb, np.float32).reshape(-1, 3)
+        out = np.zeros(rgb.shape[0], np.uint32)
+        self._ck(lib().pt_resolve_colors_noalloc(self._h, rgb.shape[0], _p(rgb), _p(out)))
+        return out
 
     def measure_fp32_peak(self):
         v = C.c_float()
