@@ -4,6 +4,7 @@
 // info size 40, 32 bpp, positive height (bottom-up), then width*height raw 0xAARRGGBB words.
 #include "host_internal.h"
 
+#include <cstdint>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -55,9 +56,17 @@ extern "C" int pt_host_read_bmp(const char *path, uint32_t **bgra_out, int *widt
     if (std::fread(hdr, 1, 54, f) != 54 || hdr[0] != 'B' || hdr[1] != 'M') { std::fclose(f); pth::set_error("not a BMP"); return -1; }
     uint32_t off; int32_t w, h; uint16_t bpp;
     std::memcpy(&off, hdr + 10, 4); std::memcpy(&w, hdr + 18, 4); std::memcpy(&h, hdr + 22, 4); std::memcpy(&bpp, hdr + 28, 2);
-    if (bpp != 32 || w <= 0 || h == 0) { std::fclose(f); pth::set_error("only 32 bpp BMPs are supported"); return -1; }
+    if (bpp != 32 || w <= 0 || h == 0 || h == INT32_MIN) { std::fclose(f); pth::set_error("only 32 bpp BMPs are supported"); return -1; }
     int ah = h < 0 ? -h : h;
-    uint32_t *px = (uint32_t *)std::malloc((size_t)w * ah * 4);
+    // the header's sizes are untrusted: the pixel array must fit between `off` and the end of the file before anything is allocated
+    std::fseek(f, 0, SEEK_END);
+    const long file_size = std::ftell(f);
+    const uint64_t need = (uint64_t)w * (uint64_t)ah * 4u;
+    if (file_size < 54 || off < 54 || (uint64_t)off > (uint64_t)file_size || need > (uint64_t)file_size - off) {
+        std::fclose(f); pth::set_error("truncated BMP"); return -1;
+    }
+    uint32_t *px = (uint32_t *)std::malloc((size_t)need);
+    if (!px) { std::fclose(f); pth::set_error("out of memory"); return -1; }
     std::fseek(f, (long)off, SEEK_SET);
     size_t got = std::fread(px, 4, (size_t)w * ah, f);
     std::fclose(f);

@@ -1,6 +1,8 @@
 // C surface of libpt_host.so (include/pt_host.h).
 #include "host_internal.h"
 
+#include <exception>
+
 #include <cstdlib>
 #include <cstring>
 
@@ -65,17 +67,30 @@ extern "C" int pt_host_scene(pt_host_world *hw, int width, int height, int lens,
 
 extern "C" int pt_host_load_glb(const char *path, float **tri_points_out, int32_t **tri_mats_out, uint32_t *n_tris,
                                 pt_material **new_materials_out, uint32_t *n_new_materials, uint32_t first_new_index) {
-    std::vector<float> pts;
-    std::vector<int32_t> mats;
-    std::vector<pt_material> materials(first_new_index);
-    if (!pth::load_glb(path, pts, mats, materials)) return -1;
-    *n_tris = (uint32_t)mats.size();
-    *tri_points_out = (float *)std::malloc(pts.size() * sizeof(float) + 4);
-    std::memcpy(*tri_points_out, pts.data(), pts.size() * sizeof(float));
-    *tri_mats_out = (int32_t *)std::malloc(mats.size() * sizeof(int32_t) + 4);
-    std::memcpy(*tri_mats_out, mats.data(), mats.size() * sizeof(int32_t));
-    *n_new_materials = (uint32_t)materials.size() - first_new_index;
-    *new_materials_out = (pt_material *)std::malloc((*n_new_materials) * sizeof(pt_material) + 4);
-    std::memcpy(*new_materials_out, materials.data() + first_new_index, (*n_new_materials) * sizeof(pt_material));
-    return 0;
+    try {
+        std::vector<float> pts;
+        std::vector<int32_t> mats;
+        std::vector<pt_material> materials(first_new_index);
+        if (!pth::load_glb(path, pts, mats, materials)) return -1;
+        // +4: never malloc(0); an empty vector's data() may be NULL, which memcpy must not see
+        auto dup = [](const void *src, size_t bytes) -> void * {
+            void *p = std::malloc(bytes + 4);
+            if (p && bytes) std::memcpy(p, src, bytes);
+            return p;
+        };
+        *n_tris = (uint32_t)mats.size();
+        *n_new_materials = (uint32_t)materials.size() - first_new_index;
+        *tri_points_out = (float *)dup(pts.data(), pts.size() * sizeof(float));
+        *tri_mats_out = (int32_t *)dup(mats.data(), mats.size() * sizeof(int32_t));
+        *new_materials_out = (pt_material *)dup(materials.data() + first_new_index, (*n_new_materials) * sizeof(pt_material));
+        if (!*tri_points_out || !*tri_mats_out || !*new_materials_out) {
+            std::free(*tri_points_out); std::free(*tri_mats_out); std::free(*new_materials_out);
+            pth::set_error("out of memory");
+            return -1;
+        }
+        return 0;
+    } catch (const std::exception &e) {          // no exception crosses the C ABI
+        pth::set_error(std::string("GLB: ") + e.what());
+        return -1;
+    }
 }

@@ -6,6 +6,7 @@
 #include <zlib.h>
 
 #include <cstdio>
+#include <exception>
 #include <cstdlib>
 #include <cstring>
 
@@ -75,7 +76,11 @@ bool load_png_rgba8(const char *path, std::vector<uint8_t> &rgba, int &w, int &h
     }
     size_t bits_pp = (size_t)channels * depth;
     size_t bpp = (bits_pp + 7) / 8;                    // filter unit
+    // IHDR is untrusted: bound the image by what the compressed data can possibly hold before anything is allocated
+    // (deflate expands by at most 1032 : 1), and keep every size computation far from wrapping
+    if (width > (1u << 16) || height > (1u << 16)) { set_error("PNG larger than 65536 pixels on a side"); return false; }
     size_t stride = ((size_t)width * bits_pp + 7) / 8;
+    if ((stride + 1) * (size_t)height > idat.size() * 1032 + 1024) { set_error("PNG image data shorter than its header claims"); return false; }
     std::vector<uint8_t> raw((stride + 1) * (size_t)height);
     uLongf out_len = (uLongf)raw.size();
     int zr = uncompress(raw.data(), &out_len, idat.data(), (uLong)idat.size());
@@ -137,10 +142,16 @@ bool load_png_rgba8(const char *path, std::vector<uint8_t> &rgba, int &w, int &h
 }  // namespace pth
 
 extern "C" int pt_host_load_png_rgba8(const char *path, uint8_t **rgba_out, int *width, int *height) {
-    std::vector<uint8_t> px; int w, h;
-    if (!pth::load_png_rgba8(path, px, w, h)) return -1;
-    uint8_t *o = (uint8_t *)std::malloc(px.size());
-    std::memcpy(o, px.data(), px.size());
-    *rgba_out = o; *width = w; *height = h;
-    return 0;
+    try {
+        std::vector<uint8_t> px; int w, h;
+        if (!pth::load_png_rgba8(path, px, w, h)) return -1;
+        uint8_t *o = (uint8_t *)std::malloc(px.size());
+        if (!o) { pth::set_error("out of memory"); return -1; }
+        std::memcpy(o, px.data(), px.size());
+        *rgba_out = o; *width = w; *height = h;
+        return 0;
+    } catch (const std::exception &e) {          // no exception crosses the C ABI
+        pth::set_error(std::string("PNG: ") + e.what());
+        return -1;
+    }
 }

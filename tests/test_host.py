@@ -220,3 +220,27 @@ def test_glb_parser_rejects_hostile_files(tmp_path):
     q = tmp_path / "neg_mesh.glb"
     q.write_bytes(_glb(doc(nodes=[{"mesh": -1}]), tri))
     assert _load_glb(q) == (0, 0)
+
+
+def test_file_readers_survive_mutated_files(tmp_path):
+    """The PNG, BMP and GLB readers take untrusted bytes.  tests/cpp/fuzz_host.cpp mutates valid files (bit flips, edge-value
+    32-bit fields, truncations, edge numbers inside the GLB's JSON) and feeds them to the C ABI, built from the host sources with
+    AddressSanitizer + UBSan and a 512 MB allocation cap: every call must load or fail cleanly -- no out-of-bounds access, no
+    undefined behaviour, no exception across the C ABI, no allocation the file's size does not justify.  (Round 2 found and
+    fixed three this way: an IHDR-sized allocation in the PNG reader, an unchecked header-sized malloc and -INT_MIN in the BMP
+    reader, memcpy from a null vector in the GLB wrapper.  150 000 iterations are clean; the test runs 6 000.)"""
+    import shutil
+    import subprocess
+    hd = os.path.join(ROOT, "pathtracer_b200", "host")
+    exe = str(tmp_path / "fuzz_host")
+    src = [os.path.join(hd, f) for f in ("worlds.cpp", "camera.cpp", "bmp.cpp", "png.cpp", "glb.cpp", "args.cpp", "host_api.cpp")]
+    cmd = ["g++", "-std=c++17", "-O1", "-g", "-fsanitize=address,undefined", "-fno-sanitize-recover=undefined",
+           "-I" + os.path.join(ROOT, "include"), "-o", exe, os.path.join(ROOT, "tests", "cpp", "fuzz_host.cpp"), *src, "-lz"]
+    b = subprocess.run(cmd, capture_output=True, text=True)
+    if b.returncode != 0 and ("asan" in b.stderr.lower() or "sanitize" in b.stderr.lower() or "ubsan" in b.stderr.lower()):
+        pytest.skip("no sanitizer runtime in this toolchain")
+    assert b.returncode == 0, b.stderr[-2000:]
+    assert shutil.which("g++")
+    env = dict(os.environ, ASAN_OPTIONS="max_allocation_size_mb=512")
+    r = subprocess.run([exe, os.path.join(ROOT, "res", "mario.glb"), str(tmp_path), "6000"], capture_output=True, text=True, env=env, timeout=600)
+    assert r.returncode == 0 and "fuzz ok" in r.stdout, (r.stdout[-1500:], r.stderr[-3000:])
