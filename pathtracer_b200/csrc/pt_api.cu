@@ -6,6 +6,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <new>
+#include <stdexcept>
 #include <string>
 #include <utility>
 #include <vector>
@@ -100,7 +102,18 @@ extern "C" const char *pt_last_error(const pt_context *ctx) { return ctx ? ctx->
 
 extern "C" int pt_destroy(pt_context *ctx);
 
+static int create_impl(const pt_config *cfg, pt_context **out);
+
 extern "C" int pt_create(const pt_config *cfg, pt_context **out) {
+    try {
+        return create_impl(cfg, out);
+    } catch (const std::exception &) {          // no C++ exception crosses the C ABI
+        if (out) *out = nullptr;
+        return PT_ERR_OOM;
+    }
+}
+
+static int create_impl(const pt_config *cfg, pt_context **out) {
     if (!out) return fail(nullptr, PT_ERR_INVALID_ARG, "pt_create: out is NULL");
     *out = nullptr;
     if (cfg && cfg->struct_size != sizeof(pt_config)) return fail(nullptr, PT_ERR_INVALID_ARG, "pt_create: struct_size mismatch");
@@ -316,8 +329,23 @@ static void launch_render(uint32_t features, unsigned blocks, cudaStream_t st, c
 #undef X
 }
 
+static int upload_scene_impl(pt_context *ctx, const pt_scene *s);
+
+// no C++ exception crosses the C ABI: the scene build allocates host vectors (materials, boxes, BVH nodes) whose sizes come from the caller
 extern "C" int pt_upload_scene(pt_context *ctx, const pt_scene *s) {
     if (!ctx || !s) return PT_ERR_INVALID_ARG;
+    try {
+        return upload_scene_impl(ctx, s);
+    } catch (const std::bad_alloc &) {
+        ctx->has_scene = false;
+        return fail(ctx, PT_ERR_OOM, "pt_upload_scene: out of host memory");
+    } catch (const std::exception &e) {
+        ctx->has_scene = false;
+        return fail(ctx, PT_ERR_INVALID_ARG, std::string("pt_upload_scene: ") + e.what());
+    }
+}
+
+static int upload_scene_impl(pt_context *ctx, const pt_scene *s) {
     if (s->struct_size != sizeof(pt_scene)) return fail(ctx, PT_ERR_INVALID_ARG, "pt_upload_scene: struct_size mismatch");
     if (s->n_materials == 0 || !s->materials) return fail(ctx, PT_ERR_INVALID_ARG, "pt_upload_scene: material 0 (the sky) is required");
     if (s->n_spheres == 0 && !(s->flags & PT_SCENE_JUST_COSINE))

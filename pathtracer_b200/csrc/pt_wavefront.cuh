@@ -321,7 +321,8 @@ struct PtWavefront {
         A.log2_pool_pixels = lP;
         const uint64_t warps = (uint64_t)A.n_my_tiles * (1024u >> lP);
         const uint64_t blocks = (warps + PT_WF_WARPS - 1) / PT_WF_WARPS;
-        if (blocks > 0x7fffffffull) { err = "pt_render: frame too large for one launch"; return PT_ERR_UNSUPPORTED; }
+        // the kernel derives its warp index from blockIdx.x * blockDim.x in 32 bits
+        if (blocks > 0xffffffffull / (PT_WF_WARPS * 32) - 1) { err = "pt_render: frame too large for one launch"; return PT_ERR_UNSUPPORTED; }
 #define X(M) if ((features & ~(uint32_t)(M)) == 0) { k_render_wf<(M)><<<(unsigned)blocks, PT_WF_WARPS * 32, 0, st>>>(S, A); *launches = 1; return PT_OK; }
         PT_RENDER_VARIANTS(X)
 #undef X
